@@ -1,0 +1,496 @@
+// libb200mel.so - C ABI (include/b200mel.h) over the sm_100a kernels.  No CPU fallback.
+#include <atomic>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "../../include/b200mel.h"
+#include "aux_kernels.cuh"
+#include "common.cuh"
+#include "generic_kernel.cuh"
+#include "plan.h"
+#ifdef B200MEL_WITH_TC
+#include "tc_kernel.cuh"
+#endif
+
+using namespace b200mel;
+
+namespace {
+
+thread_local std::string g_last_error;
+
+int fail(int code, const std::string& msg) {
+  g_last_error = msg;
+  return code;
+}
+
+int cuda_fail(cudaError_t e, const char* what) {
+  return fail(B200MEL_ERR_CUDA, std::string(what) + ": " + cudaGetErrorString(e));
+}
+
+#define CU_CHECK(expr)                                   \
+  do {                                                   \
+    cudaError_t _e = (expr);                             \
+    if (_e != cudaSuccess) return cuda_fail(_e, #expr);  \
+  } while (0)
+
+template <typename T>
+cudaError_t upload(const std::vector<T>& v, T** dptr) {
+  cudaError_t e = cudaMalloc(reinterpret_cast<void**>(dptr), v.size() * sizeof(T));
+  if (e != cudaSuccess) return e;
+  return cudaMemcpy(*dptr, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice);
+}
+
+struct DeviceGuard {
+  int prev = -1;
+  bool ok = true;
+  explicit DeviceGuard(int dev) {
+    if (cudaGetDevice(&prev) != cudaSuccess) prev = -1;
+    if (prev != dev) ok = cudaSetDevice(dev) == cudaSuccess;
+  }
+  ~DeviceGuard() {
+    if (prev >= 0) cudaSetDevice(prev);
+  }
+};
+
+}  // namespace
+
+struct b200mel_handle {
+  HostPlan plan;
+  int device = 0;
+  int sm_count = 148;
+  int max_smem_optin = 0;
+  // device tables
+  float* d_window = nullptr;
+  float* d_twiddle = nullptr;
+  float* d_post = nullptr;
+  int* d_mel_start = nullptr;
+  int* d_mel_count = nullptr;
+  int* d_mel_off = nullptr;
+  float* d_mel_w = nullptr;
+  float* d_dct = nullptr;
+  // generic kernel tiling
+  int g_warps = 8, g_ft = 32, g_halo = 0, g_per_warp_floats = 0;
+  size_t g_smem = 0;
+#ifdef B200MEL_WITH_TC
+  TcPlan tc;
+#endif
+  bool tc_ok = false;
+  std::atomic<int64_t> launches{0};
+  // e2e staging (b200mel_forward_host)
+  std::mutex host_mu;
+  void* s_pcm = nullptr;
+  size_t s_pcm_bytes = 0;
+  float* s_out = nullptr;
+  size_t s_out_bytes = 0;
+  int32_t* s_small = nullptr;  // lengths | n_frames | status
+  int64_t* s_offsets = nullptr;
+  size_t s_small_cap = 0;
+  cudaStream_t streams[3] = {nullptr, nullptr, nullptr};
+  cudaEvent_t ev_in[64];
+  bool ev_init = false;
+};
+
+extern "C" {
+
+int b200mel_version(void) { return B200MEL_VERSION; }
+
+const char* b200mel_last_error(void) { return g_last_error.c_str(); }
+
+int b200mel_create(const b200mel_config* config, int device, b200mel_handle** out_handle) {
+  if (!config || !out_handle) return fail(B200MEL_ERR_INVALID_ARGUMENT, "null argument");
+  if (config->struct_size != static_cast<int32_t>(sizeof(b200mel_config)))
+    return fail(B200MEL_ERR_INVALID_ARGUMENT, "b200mel_config.struct_size mismatch");
+  *out_handle = nullptr;
+  int n_dev = 0;
+  if (cudaGetDeviceCount(&n_dev) != cudaSuccess || n_dev <= 0) {
+    cudaGetLastError();
+    return fail(B200MEL_ERR_NO_DEVICE, "no CUDA device available: libb200mel has no CPU path");
+  }
+  if (device < 0 || device >= n_dev) return fail(B200MEL_ERR_INVALID_ARGUMENT, "device index out of range");
+
+  b200mel_handle* h = new (std::nothrow) b200mel_handle();
+  if (!h) return fail(B200MEL_ERR_CUDA, "out of host memory");
+  std::string err = build_plan(*config, h->plan);
+  if (!err.empty()) {
+    delete h;
+    return fail(B200MEL_ERR_INVALID_ARGUMENT, err);
+  }
+  h->device = device;
+  DeviceGuard guard(device);
+  if (!guard.ok) {
+    delete h;
+    return fail(B200MEL_ERR_CUDA, "cudaSetDevice failed");
+  }
+  cudaDeviceProp prop;
+  cudaError_t e = cudaGetDeviceProperties(&prop, device);
+  if (e != cudaSuccess) {
+    delete h;
+    return cuda_fail(e, "cudaGetDeviceProperties");
+  }
+  h->sm_count = prop.multiProcessorCount;
+  h->max_smem_optin = static_cast<int>(prop.sharedMemPerBlockOptin);
+
+  HostPlan& p = h->plan;
+  e = upload(p.window, &h->d_window);
+  if (e == cudaSuccess) e = upload(p.twiddle, &h->d_twiddle);
+  if (e == cudaSuccess) e = upload(p.post, &h->d_post);
+  if (e == cudaSuccess) e = upload(p.mel_start, &h->d_mel_start);
+  if (e == cudaSuccess) e = upload(p.mel_count, &h->d_mel_count);
+  if (e == cudaSuccess) e = upload(p.mel_off, &h->d_mel_off);
+  if (e == cudaSuccess) e = upload(p.mel_w, &h->d_mel_w);
+  if (e == cudaSuccess) e = upload(p.dct, &h->d_dct);
+  if (e != cudaSuccess) {
+    b200mel_destroy(h);
+    return cuda_fail(e, "uploading plan tables");
+  }
+
+  // generic kernel tiling: per-warp FFT ping-pong (2 * Nc complex) + mfcc scratch (M), and a
+  // [(FT + halo), F] feature tile; shrink until it fits the opt-in shared memory.
+  h->g_halo = p.C == 3 ? 2 : 0;
+  h->g_per_warp_floats = 4 * p.Nc + ((p.cfg.audio_feature_type == B200MEL_FEATURE_MFCC) ? p.cfg.num_mel_bins : 0);
+  h->g_per_warp_floats = (h->g_per_warp_floats + 3) & ~3;
+  int warps = 8, ft = 64;
+  const size_t budget = static_cast<size_t>(h->max_smem_optin > 0 ? h->max_smem_optin : 48 * 1024) - 1024;
+  auto smem_need = [&](int w, int f) {
+    return (static_cast<size_t>(w) * h->g_per_warp_floats + static_cast<size_t>(f + h->g_halo) * p.F) * sizeof(float);
+  };
+  while (ft > 8 && static_cast<size_t>(ft + h->g_halo) * p.F * sizeof(float) > 48 * 1024) ft /= 2;
+  while (warps > 1 && smem_need(warps, ft) > budget) warps /= 2;
+  while (ft > 1 && smem_need(warps, ft) > budget) ft /= 2;
+  if (smem_need(warps, ft) > budget) {
+    b200mel_destroy(h);
+    return fail(B200MEL_ERR_UNSUPPORTED, "configuration does not fit in shared memory");
+  }
+  h->g_warps = warps;
+  h->g_ft = ft;
+  h->g_smem = smem_need(warps, ft);
+  e = cudaFuncSetAttribute(generic_frontend_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                           static_cast<int>(h->g_smem));
+  if (e != cudaSuccess) {
+    b200mel_destroy(h);
+    return cuda_fail(e, "cudaFuncSetAttribute(generic_frontend_kernel)");
+  }
+#ifdef B200MEL_WITH_TC
+  h->tc_ok = tc_plan_build(p, h->tc, h->max_smem_optin);
+#endif
+  *out_handle = h;
+  return B200MEL_OK;
+}
+
+int b200mel_destroy(b200mel_handle* h) {
+  if (!h) return B200MEL_OK;
+  DeviceGuard guard(h->device);
+  cudaFree(h->d_window);
+  cudaFree(h->d_twiddle);
+  cudaFree(h->d_post);
+  cudaFree(h->d_mel_start);
+  cudaFree(h->d_mel_count);
+  cudaFree(h->d_mel_off);
+  cudaFree(h->d_mel_w);
+  cudaFree(h->d_dct);
+  cudaFree(h->s_pcm);
+  cudaFree(h->s_out);
+  cudaFree(h->s_small);
+  cudaFree(h->s_offsets);
+#ifdef B200MEL_WITH_TC
+  tc_plan_free(h->tc);
+#endif
+  for (auto& s : h->streams)
+    if (s) cudaStreamDestroy(s);
+  if (h->ev_init)
+    for (auto& ev : h->ev_in) cudaEventDestroy(ev);
+  delete h;
+  return B200MEL_OK;
+}
+
+int b200mel_num_frames(const b200mel_handle* h, int64_t n_samples, int64_t* n_frames) {
+  if (!h || !n_frames) return fail(B200MEL_ERR_INVALID_ARGUMENT, "null argument");
+  const int64_t Lw = h->plan.cfg.frame_length, H = h->plan.cfg.frame_step;
+  *n_frames = n_samples < Lw ? 0 : 1 + (n_samples - Lw) / H;
+  return B200MEL_OK;
+}
+
+int b200mel_feature_shape(const b200mel_handle* h, int32_t* frequency_dim, int32_t* feature_dim, int32_t* fft_length) {
+  if (!h) return fail(B200MEL_ERR_INVALID_ARGUMENT, "null handle");
+  if (frequency_dim) *frequency_dim = h->plan.F;
+  if (feature_dim) *feature_dim = h->plan.C;
+  if (fft_length) *fft_length = h->plan.N;
+  return B200MEL_OK;
+}
+
+int b200mel_mel_weights(const b200mel_handle* h, float* out_host) {
+  if (!h || !out_host) return fail(B200MEL_ERR_INVALID_ARGUMENT, "null argument");
+  if (h->plan.mel_dense.empty()) return fail(B200MEL_ERR_INVALID_ARGUMENT, "feature type has no mel filterbank");
+  std::memcpy(out_host, h->plan.mel_dense.data(), h->plan.mel_dense.size() * sizeof(float));
+  return B200MEL_OK;
+}
+
+int b200mel_tc_supported(const b200mel_handle* h) { return (h && h->tc_ok) ? 1 : 0; }
+
+int64_t b200mel_launch_count(const b200mel_handle* h) { return h ? h->launches.load() : 0; }
+
+static void fill_params(const b200mel_handle* h, KernelParams& kp) {
+  const HostPlan& p = h->plan;
+  std::memset(&kp, 0, sizeof(kp));
+  kp.Lw = p.cfg.frame_length;
+  kp.H = p.cfg.frame_step;
+  kp.N = p.N;
+  kp.K = p.K;
+  kp.Lw_eff = p.Lw_eff;
+  kp.Nc = p.Nc;
+  kp.even = p.even;
+  kp.n_radices = static_cast<int>(p.radices.size());
+  for (size_t i = 0; i < p.radices.size(); ++i) kp.radices[i] = p.radices[i];
+  kp.window = h->d_window;
+  kp.twiddle = reinterpret_cast<const float2*>(h->d_twiddle);
+  kp.post = reinterpret_cast<const float2*>(h->d_post);
+  kp.feature_type = p.cfg.audio_feature_type;
+  kp.M = p.cfg.num_mel_bins;
+  kp.n_mfcc = p.n_mfcc_eff;
+  kp.F = p.F;
+  kp.C = p.C;
+  kp.epsilon = p.cfg.epsilon;
+  kp.mel_start = h->d_mel_start;
+  kp.mel_count = h->d_mel_count;
+  kp.mel_off = h->d_mel_off;
+  kp.mel_w = h->d_mel_w;
+  kp.dct = h->d_dct;
+  kp.n_masks_f = p.n_masks_f;
+  kp.n_masks_t = p.n_masks_t;
+  kp.sa_F = p.cfg.sa_F;
+  kp.sa_T = p.cfg.sa_T;
+  kp.sa_p = p.cfg.sa_p;
+  kp.frames_per_tile = h->g_ft;
+  kp.halo = h->g_halo;
+  kp.warps = h->g_warps;
+  kp.smem_per_warp_floats = h->g_per_warp_floats;
+}
+
+int b200mel_forward(b200mel_handle* h, const void* pcm, int32_t pcm_dtype, const int64_t* offsets,
+                    const int32_t* lengths, int32_t batch, int64_t row_stride, float* out, int64_t t_max,
+                    int32_t* n_frames, const int32_t* mask_table, uint64_t seed, uint64_t first_utterance_id,
+                    int32_t* status, int32_t kernel, void* stream) {
+  if (!h) return fail(B200MEL_ERR_INVALID_ARGUMENT, "null handle");
+  if (batch < 0 || t_max < 0) return fail(B200MEL_ERR_INVALID_ARGUMENT, "negative batch or t_max");
+  if (pcm_dtype != B200MEL_PCM_I16 && pcm_dtype != B200MEL_PCM_F32)
+    return fail(B200MEL_ERR_INVALID_ARGUMENT, "pcm_dtype must be B200MEL_PCM_I16 or B200MEL_PCM_F32");
+  if (kernel < B200MEL_KERNEL_AUTO || kernel > B200MEL_KERNEL_TC)
+    return fail(B200MEL_ERR_INVALID_ARGUMENT, "unknown kernel selector");
+  if (kernel == B200MEL_KERNEL_TC && !h->tc_ok)
+    return fail(B200MEL_ERR_UNSUPPORTED, "the tensor-core kernel does not support this configuration");
+  if (batch == 0) return B200MEL_OK;
+  if (!lengths || (!pcm) || (t_max > 0 && !out)) return fail(B200MEL_ERR_INVALID_ARGUMENT, "null buffer");
+  if (batch > 65535) return fail(B200MEL_ERR_UNSUPPORTED, "batch > 65535: split the call");
+  if (t_max > (int64_t{1} << 30)) return fail(B200MEL_ERR_UNSUPPORTED, "t_max too large");
+  DeviceGuard guard(h->device);
+  if (!guard.ok) return fail(B200MEL_ERR_CUDA, "cudaSetDevice failed");
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+
+  KernelParams kp;
+  fill_params(h, kp);
+  kp.pcm = pcm;
+  kp.offsets = offsets;
+  kp.lengths = lengths;
+  kp.row_stride = row_stride;
+  kp.pcm_is_f32 = pcm_dtype == B200MEL_PCM_F32;
+  kp.batch = batch;
+  kp.out = out;
+  kp.t_max = t_max;
+  kp.n_frames = n_frames;
+  kp.status = status;
+  kp.mask_table = mask_table;
+  kp.seed = seed;
+  kp.first_utt = first_utterance_id;
+
+  if (t_max == 0) {
+    // nothing to write but n_frames: one tile per utterance still reports the frame counts
+    if (!n_frames) return B200MEL_OK;
+  }
+#ifdef B200MEL_WITH_TC
+  if (h->tc_ok && kernel != B200MEL_KERNEL_GENERIC && t_max > 0) {
+    int rc = tc_launch(h->tc, kp, h->sm_count, st);
+    if (rc != 0) return cuda_fail(cudaGetLastError(), "tc_frontend_kernel launch");
+    h->launches.fetch_add(1);
+    return B200MEL_OK;
+  }
+#endif
+  int64_t tiles = (t_max + h->g_ft - 1) / h->g_ft;
+  if (tiles == 0) tiles = 1;
+  dim3 grid(static_cast<unsigned>(tiles), static_cast<unsigned>(batch));
+  generic_frontend_kernel<<<grid, h->g_warps * 32, h->g_smem, st>>>(kp);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return cuda_fail(e, "generic_frontend_kernel launch");
+  h->launches.fetch_add(1);
+  return B200MEL_OK;
+}
+
+int b200mel_forward_host(b200mel_handle* h, const void* pcm_host, int32_t pcm_dtype, const int64_t* offsets_host,
+                         const int32_t* lengths_host, int32_t batch, int64_t row_stride, int64_t total_samples,
+                         float* out_host, int64_t t_max, int32_t* n_frames_host, uint64_t seed,
+                         uint64_t first_utterance_id, int32_t kernel) {
+  if (!h) return fail(B200MEL_ERR_INVALID_ARGUMENT, "null handle");
+  if (batch < 0 || t_max < 0 || total_samples < 0) return fail(B200MEL_ERR_INVALID_ARGUMENT, "negative size");
+  if (batch == 0) return B200MEL_OK;
+  if (!pcm_host || !lengths_host || (t_max > 0 && !out_host)) return fail(B200MEL_ERR_INVALID_ARGUMENT, "null buffer");
+  if (pcm_dtype != B200MEL_PCM_I16 && pcm_dtype != B200MEL_PCM_F32)
+    return fail(B200MEL_ERR_INVALID_ARGUMENT, "pcm_dtype must be B200MEL_PCM_I16 or B200MEL_PCM_F32");
+  const size_t esz = pcm_dtype == B200MEL_PCM_F32 ? 4 : 2;
+  if (!offsets_host && total_samples < static_cast<int64_t>(batch) * row_stride)
+    return fail(B200MEL_ERR_INVALID_ARGUMENT, "total_samples < batch * row_stride");
+  std::lock_guard<std::mutex> lock(h->host_mu);
+  DeviceGuard guard(h->device);
+  if (!guard.ok) return fail(B200MEL_ERR_CUDA, "cudaSetDevice failed");
+  for (auto& s : h->streams)
+    if (!s) CU_CHECK(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
+  if (!h->ev_init) {
+    for (auto& ev : h->ev_in) CU_CHECK(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+    h->ev_init = true;
+  }
+  const HostPlan& p = h->plan;
+  const size_t pcm_bytes = static_cast<size_t>(total_samples) * esz;
+  const size_t per_utt_out = static_cast<size_t>(t_max) * p.F * p.C;
+  const size_t out_bytes = per_utt_out * batch * sizeof(float);
+  if (pcm_bytes > h->s_pcm_bytes) {
+    cudaFree(h->s_pcm);
+    h->s_pcm = nullptr;
+    h->s_pcm_bytes = 0;
+    CU_CHECK(cudaMalloc(&h->s_pcm, pcm_bytes + 256));
+    h->s_pcm_bytes = pcm_bytes;
+  }
+  if (out_bytes > h->s_out_bytes) {
+    cudaFree(h->s_out);
+    h->s_out = nullptr;
+    h->s_out_bytes = 0;
+    CU_CHECK(cudaMalloc(reinterpret_cast<void**>(&h->s_out), out_bytes + 256));
+    h->s_out_bytes = out_bytes;
+  }
+  if (static_cast<size_t>(batch) > h->s_small_cap) {
+    cudaFree(h->s_small);
+    cudaFree(h->s_offsets);
+    h->s_small = nullptr;
+    h->s_offsets = nullptr;
+    h->s_small_cap = 0;
+    CU_CHECK(cudaMalloc(reinterpret_cast<void**>(&h->s_small), (2 * static_cast<size_t>(batch) + 4) * sizeof(int32_t)));
+    CU_CHECK(cudaMalloc(reinterpret_cast<void**>(&h->s_offsets), static_cast<size_t>(batch) * sizeof(int64_t)));
+    h->s_small_cap = batch;
+  }
+  int32_t* d_len = h->s_small;
+  int32_t* d_nf = h->s_small + batch;
+  cudaStream_t s_in = h->streams[0], s_k = h->streams[1], s_out = h->streams[2];
+  CU_CHECK(cudaMemcpyAsync(d_len, lengths_host, batch * sizeof(int32_t), cudaMemcpyHostToDevice, s_in));
+  if (offsets_host)
+    CU_CHECK(cudaMemcpyAsync(h->s_offsets, offsets_host, batch * sizeof(int64_t), cudaMemcpyHostToDevice, s_in));
+
+  // Chunked 3-stage pipeline: H2D(chunk i+1) | kernel(chunk i) | D2H(chunk i-1) on three streams,
+  // so PCIe traffic in both directions overlaps the kernel.
+  int n_chunks = batch < 8 ? 1 : 8;
+  if (n_chunks > 32) n_chunks = 32;
+  const char* src = static_cast<const char*>(pcm_host);
+  char* dst = static_cast<char*>(h->s_pcm);
+  for (int c = 0; c < n_chunks; ++c) {
+    const int b0 = static_cast<int>(static_cast<int64_t>(batch) * c / n_chunks);
+    const int b1 = static_cast<int>(static_cast<int64_t>(batch) * (c + 1) / n_chunks);
+    if (b1 <= b0) continue;
+    int64_t lo, hi;
+    if (offsets_host) {
+      lo = INT64_MAX;
+      hi = 0;
+      for (int b = b0; b < b1; ++b) {
+        if (offsets_host[b] < 0 || offsets_host[b] + lengths_host[b] > total_samples)
+          return fail(B200MEL_ERR_INVALID_ARGUMENT, "offsets/lengths outside total_samples");
+        lo = offsets_host[b] < lo ? offsets_host[b] : lo;
+        int64_t end = offsets_host[b] + lengths_host[b];
+        hi = end > hi ? end : hi;
+      }
+      if (hi < lo) hi = lo;
+    } else {
+      lo = static_cast<int64_t>(b0) * row_stride;
+      hi = static_cast<int64_t>(b1) * row_stride;
+    }
+    if (hi > lo)
+      CU_CHECK(cudaMemcpyAsync(dst + lo * esz, src + lo * esz, static_cast<size_t>(hi - lo) * esz,
+                               cudaMemcpyHostToDevice, s_in));
+    CU_CHECK(cudaEventRecord(h->ev_in[2 * c], s_in));
+    CU_CHECK(cudaStreamWaitEvent(s_k, h->ev_in[2 * c], 0));
+    const int64_t* d_off = offsets_host ? h->s_offsets + b0 : nullptr;
+    const char* d_pcm = offsets_host ? dst : dst + static_cast<int64_t>(b0) * row_stride * esz;
+    int rc = b200mel_forward(h, d_pcm, pcm_dtype, d_off, d_len + b0, b1 - b0, row_stride,
+                             h->s_out + per_utt_out * b0, t_max, d_nf + b0, nullptr, seed,
+                             first_utterance_id + static_cast<uint64_t>(b0), nullptr, kernel, s_k);
+    if (rc != B200MEL_OK) return rc;
+    CU_CHECK(cudaEventRecord(h->ev_in[2 * c + 1], s_k));
+    CU_CHECK(cudaStreamWaitEvent(s_out, h->ev_in[2 * c + 1], 0));
+    if (per_utt_out > 0)
+      CU_CHECK(cudaMemcpyAsync(out_host + per_utt_out * b0, h->s_out + per_utt_out * b0,
+                               per_utt_out * (b1 - b0) * sizeof(float), cudaMemcpyDeviceToHost, s_out));
+  }
+  if (n_frames_host) {
+    CU_CHECK(cudaStreamSynchronize(s_k));
+    CU_CHECK(cudaMemcpyAsync(n_frames_host, d_nf, batch * sizeof(int32_t), cudaMemcpyDeviceToHost, s_k));
+  }
+  CU_CHECK(cudaStreamSynchronize(s_in));
+  CU_CHECK(cudaStreamSynchronize(s_k));
+  CU_CHECK(cudaStreamSynchronize(s_out));
+  return B200MEL_OK;
+}
+
+int b200mel_specaug_draw(const int32_t* num_time, int32_t batch, int32_t v, int32_t F, int32_t m_F, int32_t T,
+                         float p, int32_t m_T, uint64_t seed, uint64_t first_utterance_id, int32_t* table,
+                         int32_t* status, void* stream) {
+  if (batch < 0) return fail(B200MEL_ERR_INVALID_ARGUMENT, "negative batch");
+  // enable flags of spec_augment (data.py:267-269)
+  int nf = (F != 0 && m_F != 0) ? m_F : 0;
+  int nt = (T != 0 && p != 0.0f && m_T != 0) ? m_T : 0;
+  if (nf < 0 || nt < 0 || F < 0 || T < 0) return fail(B200MEL_ERR_INVALID_ARGUMENT, "negative SpecAugment parameter");
+  if (nf + nt > kMaxMasks) return fail(B200MEL_ERR_UNSUPPORTED, "more than 16 SpecAugment masks");
+  if (batch == 0 || nf + nt == 0) return B200MEL_OK;
+  if (!num_time || !table) return fail(B200MEL_ERR_INVALID_ARGUMENT, "null buffer");
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  specaug_draw_kernel<<<(batch + 127) / 128, 128, 0, st>>>(num_time, batch, v, F, nf, T, p, nt, seed,
+                                                          first_utterance_id, table, status);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return cuda_fail(e, "specaug_draw_kernel launch");
+  return B200MEL_OK;
+}
+
+int b200mel_specaug_apply(const float* in, float* out, int32_t batch, int64_t t_max, int32_t v, int32_t channels,
+                          const int32_t* table, int32_t m_F, int32_t m_T, void* stream) {
+  if (batch < 0 || t_max < 0 || v < 0 || channels < 0 || m_F < 0 || m_T < 0)
+    return fail(B200MEL_ERR_INVALID_ARGUMENT, "negative size");
+  if (m_F + m_T > kMaxMasks) return fail(B200MEL_ERR_UNSUPPORTED, "more than 16 SpecAugment masks");
+  if (batch > 65535) return fail(B200MEL_ERR_UNSUPPORTED, "batch > 65535: split the call");
+  int64_t per = t_max * v * channels;
+  if (batch == 0 || per == 0) return B200MEL_OK;
+  if (!in || !out || (m_F + m_T > 0 && !table)) return fail(B200MEL_ERR_INVALID_ARGUMENT, "null buffer");
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  int64_t blocks = (per + 255) / 256;
+  if (blocks > 1184) blocks = 1184;
+  specaug_apply_kernel<<<dim3(static_cast<unsigned>(blocks), batch), 256, 0, st>>>(in, out, t_max, v, channels, table,
+                                                                                  m_F, m_T);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return cuda_fail(e, "specaug_apply_kernel launch");
+  return B200MEL_OK;
+}
+
+int b200mel_delta(const float* in, float* out, const int32_t* n_frames, int32_t batch, int64_t t_max, int32_t v,
+                  void* stream) {
+  if (batch < 0 || t_max < 0 || v < 0) return fail(B200MEL_ERR_INVALID_ARGUMENT, "negative size");
+  if (batch > 65535) return fail(B200MEL_ERR_UNSUPPORTED, "batch > 65535: split the call");
+  int64_t per = t_max * v;
+  if (batch == 0 || per == 0) return B200MEL_OK;
+  if (!in || !out) return fail(B200MEL_ERR_INVALID_ARGUMENT, "null buffer");
+  if (in == out) return fail(B200MEL_ERR_INVALID_ARGUMENT, "delta cannot run in place");
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  int64_t blocks = (per * 3 + 255) / 256;
+  if (blocks > 1184) blocks = 1184;
+  delta_kernel<<<dim3(static_cast<unsigned>(blocks), batch), 256, 0, st>>>(in, out, n_frames, t_max, v);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return cuda_fail(e, "delta_kernel launch");
+  return B200MEL_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,284 @@
+// Generic fused front-end kernel: any (frame_length, frame_step, fft_length, mel, mfcc) set.
+//
+// One CTA = one tile of `frames_per_tile` consecutive frames of one utterance (+`halo` earlier
+// frames when delta features need them).  Each warp owns whole frames: it gathers the frame from
+// global memory (the 2x overlap between neighbouring frames is absorbed by L1/L2), windows it,
+// runs a Stockham auto-sort mixed-radix FFT in its private shared-memory ping-pong buffers
+// (packed real transform: complex N/2 + split post-pass for even N), and reduces power -> mel
+// (band form, <= ~9 taps per bin for the shipped configs) -> log(+eps) [-> DCT-II] into a
+// feature tile in shared memory.  The CTA then streams the tile to HBM once, applying the
+// SpecAugment 0/1 masks and delta / delta-delta on the way out, and zero-fills padding frames.
+// Only the [B, T, F, C] output ever reaches HBM (reference: five materialised intermediates,
+// speech_recognition/data.py:172-183).
+#pragma once
+
+#include "common.cuh"
+
+namespace b200mel {
+
+__device__ __forceinline__ float2 cmul(float2 a, float2 b) {
+  return make_float2(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x);
+}
+__device__ __forceinline__ float2 cadd(float2 a, float2 b) { return make_float2(a.x + b.x, a.y + b.y); }
+__device__ __forceinline__ float2 csub(float2 a, float2 b) { return make_float2(a.x - b.x, a.y - b.y); }
+// multiply by -i / +i
+__device__ __forceinline__ float2 mul_mi(float2 a) { return make_float2(a.y, -a.x); }
+__device__ __forceinline__ float2 mul_pi(float2 a) { return make_float2(-a.y, a.x); }
+
+template <int R>
+__device__ __forceinline__ void butterfly(float2* v);
+
+template <>
+__device__ __forceinline__ void butterfly<2>(float2* v) {
+  float2 a = v[0], b = v[1];
+  v[0] = cadd(a, b);
+  v[1] = csub(a, b);
+}
+template <>
+__device__ __forceinline__ void butterfly<4>(float2* v) {
+  float2 a = cadd(v[0], v[2]), b = csub(v[0], v[2]);
+  float2 c = cadd(v[1], v[3]), d = mul_mi(csub(v[1], v[3]));
+  v[0] = cadd(a, c);
+  v[1] = cadd(b, d);
+  v[2] = csub(a, c);
+  v[3] = csub(b, d);
+}
+template <>
+__device__ __forceinline__ void butterfly<3>(float2* v) {
+  const float s3 = 0.86602540378443864676f;
+  float2 s = cadd(v[1], v[2]), d = csub(v[1], v[2]);
+  float2 t = make_float2(v[0].x - 0.5f * s.x, v[0].y - 0.5f * s.y);
+  float2 u = mul_mi(make_float2(s3 * d.x, s3 * d.y));
+  v[0] = cadd(v[0], s);
+  v[1] = cadd(t, u);
+  v[2] = csub(t, u);
+}
+template <>
+__device__ __forceinline__ void butterfly<5>(float2* v) {
+  const float c1 = 0.30901699437494742410f, c2 = -0.80901699437494742410f;
+  const float s1 = 0.95105651629515357212f, s2 = 0.58778525229247312917f;
+  float2 a1 = cadd(v[1], v[4]), a2 = cadd(v[2], v[3]);
+  float2 b1 = csub(v[1], v[4]), b2 = csub(v[2], v[3]);
+  float2 p1 = make_float2(v[0].x + c1 * a1.x + c2 * a2.x, v[0].y + c1 * a1.y + c2 * a2.y);
+  float2 p2 = make_float2(v[0].x + c2 * a1.x + c1 * a2.x, v[0].y + c2 * a1.y + c1 * a2.y);
+  float2 q1 = mul_mi(make_float2(s1 * b1.x + s2 * b2.x, s1 * b1.y + s2 * b2.y));
+  float2 q2 = mul_mi(make_float2(s2 * b1.x - s1 * b2.x, s2 * b1.y - s1 * b2.y));
+  v[0] = make_float2(v[0].x + a1.x + a2.x, v[0].y + a1.y + a2.y);
+  v[1] = cadd(p1, q1);
+  v[4] = csub(p1, q1);
+  v[2] = cadd(p2, q2);
+  v[3] = csub(p2, q2);
+}
+
+// One Stockham pass of radix R over Nc points held by one warp.  Ns = product of the radices
+// already applied.  twiddle[j] = W_Nc^j.
+template <int R>
+__device__ __forceinline__ void stockham_pass(const float2* __restrict__ in, float2* __restrict__ out,
+                                              int Nc, int Ns, const float2* __restrict__ tw, int lane) {
+  const int m = Nc / R;
+  const int tstride = Nc / (Ns * R);
+  for (int j = lane; j < m; j += 32) {
+    const int k = j % Ns;
+    float2 v[R];
+#pragma unroll
+    for (int q = 0; q < R; ++q) v[q] = in[j + q * m];
+    if (Ns > 1) {
+#pragma unroll
+      for (int q = 1; q < R; ++q) v[q] = cmul(v[q], __ldg(&tw[q * k * tstride]));
+    }
+    butterfly<R>(v);
+    const int j0 = (j - k) * R + k;
+#pragma unroll
+    for (int q = 0; q < R; ++q) out[j0 + q * Ns] = v[q];
+  }
+}
+
+// Radix-r pass for any other prime r: naive O(r^2) butterfly straight from shared memory.
+__device__ __forceinline__ void stockham_pass_any(const float2* __restrict__ in, float2* __restrict__ out,
+                                                  int Nc, int Ns, int r, const float2* __restrict__ tw,
+                                                  int lane) {
+  const int m = Nc / r;
+  const int tstride = Nc / (Ns * r);
+  const int rstride = Nc / r;
+  for (int j = lane; j < m; j += 32) {
+    const int k = j % Ns;
+    const int j0 = (j - k) * r + k;
+    for (int qo = 0; qo < r; ++qo) {
+      float2 acc = make_float2(0.f, 0.f);
+      for (int qi = 0; qi < r; ++qi) {
+        int ti = (qi * k * tstride + ((qi * qo) % r) * rstride) % Nc;
+        acc = cadd(acc, cmul(in[j + qi * m], __ldg(&tw[ti])));
+      }
+      out[j0 + qo * Ns] = acc;
+    }
+  }
+}
+
+__device__ __forceinline__ float load_sample(const void* pcm, int is_f32, int64_t idx) {
+  if (is_f32) return __ldg(reinterpret_cast<const float*>(pcm) + idx);
+  // int16 / 32768 (data.py:98,104): exact, 2^-15 is a power of two
+  return static_cast<float>(__ldg(reinterpret_cast<const short*>(pcm) + idx)) * (1.0f / 32768.0f);
+}
+
+__global__ void __launch_bounds__(256) generic_frontend_kernel(const KernelParams p) {
+  extern __shared__ __align__(16) float smem[];
+  __shared__ int32_t s_table[2 * kMaxMasks];
+
+  const int b = blockIdx.y;
+  const int tile = blockIdx.x;
+  const int lane = threadIdx.x & 31;
+  const int warp = threadIdx.x >> 5;
+  const int FT = p.frames_per_tile;
+  const int halo = p.halo;
+  const int F = p.F;
+  const int len = p.lengths[b];
+  const int n_fr = frames_of(len, p.Lw, p.H);
+  const int64_t base = p.offsets ? p.offsets[b] : static_cast<int64_t>(b) * p.row_stride;
+  const int t0 = tile * FT;
+
+  float* tile_feat = smem + static_cast<size_t>(p.warps) * p.smem_per_warp_floats;  // [(FT+halo)][F]
+  float* wbuf = smem + static_cast<size_t>(warp) * p.smem_per_warp_floats;
+  float2* bufA = reinterpret_cast<float2*>(wbuf);
+  float2* bufB = bufA + p.Nc;
+  float* scratch = reinterpret_cast<float*>(bufB + p.Nc);  // [M] (mfcc only)
+
+  const int n_masks = p.n_masks_f + p.n_masks_t;
+  if (threadIdx.x == 0) {
+    if (tile == 0 && p.n_frames) p.n_frames[b] = n_fr;
+    if (n_masks > 0) {
+      if (p.mask_table) {
+        for (int i = 0; i < 2 * n_masks; ++i) s_table[i] = p.mask_table[static_cast<size_t>(b) * 2 * n_masks + i];
+      } else {
+        int bad = specaug_draw_table(n_fr, F, p.sa_F, p.n_masks_f, p.sa_T, p.sa_p, p.n_masks_t, p.seed,
+                                     p.first_utt + static_cast<uint64_t>(b), s_table);
+        if (bad && tile == 0 && p.status) atomicOr(p.status, 1);
+      }
+    }
+  }
+
+  // ---- phase 1: one warp per frame -> feature tile -----------------------------------------
+  for (int f = warp; f < FT + halo; f += p.warps) {
+    const int t = t0 - halo + f;
+    float* row = tile_feat + static_cast<size_t>(f) * F;
+    if (t < 0 || t >= n_fr) {
+      for (int j = lane; j < F; j += 32) row[j] = 0.0f;
+      continue;
+    }
+    const int64_t s0 = base + static_cast<int64_t>(t) * p.H;
+    // gather + window (+ crop / zero-pad to N)
+    if (p.even) {
+      for (int j = lane; j < p.Nc; j += 32) {
+        int n0 = 2 * j, n1 = 2 * j + 1;
+        float x0 = n0 < p.Lw_eff ? load_sample(p.pcm, p.pcm_is_f32, s0 + n0) * __ldg(&p.window[n0]) : 0.0f;
+        float x1 = n1 < p.Lw_eff ? load_sample(p.pcm, p.pcm_is_f32, s0 + n1) * __ldg(&p.window[n1]) : 0.0f;
+        bufA[j] = make_float2(x0, x1);
+      }
+    } else {
+      for (int j = lane; j < p.Nc; j += 32) {
+        float x0 = j < p.Lw_eff ? load_sample(p.pcm, p.pcm_is_f32, s0 + j) * __ldg(&p.window[j]) : 0.0f;
+        bufA[j] = make_float2(x0, 0.0f);
+      }
+    }
+    __syncwarp();
+    float2* src = bufA;
+    float2* dst = bufB;
+    int Ns = 1;
+    for (int r = 0; r < p.n_radices; ++r) {
+      const int R = p.radices[r];
+      switch (R) {
+        case 4: stockham_pass<4>(src, dst, p.Nc, Ns, p.twiddle, lane); break;
+        case 2: stockham_pass<2>(src, dst, p.Nc, Ns, p.twiddle, lane); break;
+        case 3: stockham_pass<3>(src, dst, p.Nc, Ns, p.twiddle, lane); break;
+        case 5: stockham_pass<5>(src, dst, p.Nc, Ns, p.twiddle, lane); break;
+        default: stockham_pass_any(src, dst, p.Nc, Ns, R, p.twiddle, lane); break;
+      }
+      Ns *= R;
+      float2* tmp = src; src = dst; dst = tmp;
+      __syncwarp();
+    }
+    // src = Z (complex spectrum of the packed sequence); dst is free: power / magnitude -> dst
+    float* spec = reinterpret_cast<float*>(dst);
+    const bool want_mag = p.feature_type == B200MEL_FEATURE_SPECTROGRAM;
+    for (int k = lane; k < p.K; k += 32) {
+      float2 X;
+      if (p.even) {
+        float2 A = src[k == p.Nc ? 0 : k];
+        float2 Bc = src[k == 0 ? 0 : p.Nc - k];
+        Bc.y = -Bc.y;
+        float2 E = make_float2(0.5f * (A.x + Bc.x), 0.5f * (A.y + Bc.y));
+        float2 O = mul_mi(make_float2(0.5f * (A.x - Bc.x), 0.5f * (A.y - Bc.y)));
+        X = cadd(E, cmul(__ldg(&p.post[k]), O));
+      } else {
+        X = src[k];
+      }
+      float pw = X.x * X.x + X.y * X.y;
+      spec[k] = want_mag ? sqrtf(pw) : pw;
+    }
+    __syncwarp();
+    if (want_mag) {
+      for (int k = lane; k < p.K; k += 32) row[k] = spec[k];
+    } else {
+      const bool mfcc = p.feature_type == B200MEL_FEATURE_MFCC;
+      float* dest = mfcc ? scratch : row;
+      for (int m = lane; m < p.M; m += 32) {
+        const int st = __ldg(&p.mel_start[m]), cnt = __ldg(&p.mel_count[m]), off = __ldg(&p.mel_off[m]);
+        float acc = 0.0f;
+        for (int i = 0; i < cnt; ++i) acc = fmaf(spec[st + i], __ldg(&p.mel_w[off + i]), acc);
+        dest[m] = logf(acc + p.epsilon);
+      }
+      if (mfcc) {
+        __syncwarp();
+        for (int c = lane; c < p.n_mfcc; c += 32) {
+          float acc = 0.0f;
+          for (int m = 0; m < p.M; ++m) acc = fmaf(scratch[m], __ldg(&p.dct[m * p.n_mfcc + c]), acc);
+          row[c] = acc;
+        }
+      }
+    }
+    __syncwarp();
+  }
+  __syncthreads();
+
+  // ---- phase 2: tile -> HBM with masks, delta, padding --------------------------------------
+  const int C = p.C;
+  const int64_t t_end = (static_cast<int64_t>(t0) + FT < p.t_max) ? t0 + FT : p.t_max;
+  const int rows = static_cast<int>(t_end - t0);
+  const int64_t total = static_cast<int64_t>(rows) * F * C;
+  float* outp = p.out + (static_cast<int64_t>(b) * p.t_max + t0) * F * C;
+  for (int64_t o = threadIdx.x; o < total; o += blockDim.x) {
+    const int c = static_cast<int>(o % C);
+    const int e = static_cast<int>(o / C);
+    const int j = e % F;
+    const int i = e / F;
+    const int t = t0 + i;
+    float val = 0.0f;
+    if (t < n_fr) {
+      const float* r0 = tile_feat + static_cast<size_t>(i + halo) * F + j;
+      float x0 = r0[0];
+      if (n_masks) x0 *= mask_value(s_table, p.n_masks_f, p.n_masks_t, t, j);
+      if (c == 0) {
+        val = x0;
+      } else {
+        float x1 = 0.0f, x2 = 0.0f;
+        if (t >= 1) {
+          x1 = r0[-F];
+          if (n_masks) x1 *= mask_value(s_table, p.n_masks_f, p.n_masks_t, t - 1, j);
+        }
+        float d0 = x0 - x1;
+        if (c == 1) {
+          val = d0;
+        } else {
+          if (t >= 2) {
+            x2 = r0[-2 * F];
+            if (n_masks) x2 *= mask_value(s_table, p.n_masks_f, p.n_masks_t, t - 2, j);
+          }
+          float d1 = x1 - x2;
+          val = d0 - d1;
+        }
+      }
+    }
+    outp[o] = val;
+  }
+}
+
+}  // namespace b200mel

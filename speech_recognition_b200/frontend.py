@@ -1,0 +1,312 @@
+"""FeatureFrontend: the batched, fused form of the reference's feature maps.
+
+The reference maps a per-example callable over a tf.data pipeline and pads afterwards
+(run/train.py:88-116, 192-197).  This class does the same work for a whole batch in one kernel
+launch on a B200: feature (data.py:122-241) -> SpecAugment masks (data.py:282-301) -> delta
+(data.py:310-328) -> zero padding to Tmax, writing only [B, Tmax, F, C] to HBM.
+
+torch is used for device memory and streams only; the arithmetic is in lib/libb200mel.so.
+"""
+import ctypes
+from typing import Optional, Sequence, Tuple, Union
+
+import numpy as np
+import torch
+
+from . import _lib
+
+
+def _sa_get(sa, key):
+    if sa is None:
+        return None
+    if isinstance(sa, dict):
+        return sa.get(key)
+    return getattr(sa, key, None)
+
+
+def _ptr(t: Optional[torch.Tensor]):
+    return ctypes.c_void_p(t.data_ptr()) if t is not None else None
+
+
+class FeatureFrontend:
+    """One immutable plan (window, twiddles, float32 mel filterbank in TF's op order, DCT matrix)
+    on one CUDA device.  Parameter names are the YAML keys of ``resources/configs/*_config.yml``
+    (configs/data_config.py:23-54)."""
+
+    def __init__(self, audio_feature_type: str, sample_rate: int, frame_length: int, frame_step: int,
+                 fft_length: Optional[int] = None, num_mel_bins: Optional[int] = None,
+                 num_mfcc: Optional[int] = None, lower_edge_hertz: Optional[float] = None,
+                 upper_edge_hertz: Optional[float] = None, epsilon: float = 1e-12,
+                 use_delta_accelerate: bool = False, spec_augment=None,
+                 device: Union[None, int, str, torch.device] = None):
+        if audio_feature_type not in _lib.FEATURE_TYPES:
+            raise ValueError("audio_feature_type must be one of %s" % sorted(_lib.FEATURE_TYPES))
+        if _sa_get(spec_augment, "W"):
+            raise NotImplementedError(
+                "SpecAugment time warping (data.py:275-280) is outside this front-end's scope; "
+                "set W to null as every shipped config does")
+        if not torch.cuda.is_available():
+            raise RuntimeError("speech_recognition_b200 needs a CUDA device: there is no CPU fallback")
+        dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        if dev.type != "cuda":
+            raise RuntimeError("FeatureFrontend runs on CUDA devices only (got %s)" % dev)
+        if dev.index is None:
+            dev = torch.device("cuda", torch.cuda.current_device())
+        self.device = dev
+        sa_on = bool(_sa_get(spec_augment, "enable")) if spec_augment is not None else False
+        cfg = _lib.B200MelConfig()
+        cfg.struct_size = ctypes.sizeof(_lib.B200MelConfig)
+        cfg.audio_feature_type = _lib.FEATURE_TYPES[audio_feature_type]
+        cfg.sample_rate = int(sample_rate)
+        cfg.frame_length = int(frame_length)
+        cfg.frame_step = int(frame_step)
+        cfg.fft_length = int(fft_length) if fft_length else 0
+        cfg.num_mel_bins = int(num_mel_bins or 0)
+        cfg.num_mfcc = int(num_mfcc or 0)
+        cfg.lower_edge_hertz = float(lower_edge_hertz or 0.0)
+        cfg.upper_edge_hertz = float(upper_edge_hertz or 0.0)
+        cfg.epsilon = float(epsilon)
+        cfg.use_delta_accelerate = 1 if use_delta_accelerate else 0
+        cfg.spec_augment_enable = 1 if sa_on else 0
+        cfg.sa_F = int(_sa_get(spec_augment, "F") or 0) if sa_on else 0
+        cfg.sa_m_F = int(_sa_get(spec_augment, "m_F") or 0) if sa_on else 0
+        cfg.sa_T = int(_sa_get(spec_augment, "T") or 0) if sa_on else 0
+        cfg.sa_m_T = int(_sa_get(spec_augment, "m_T") or 0) if sa_on else 0
+        cfg.sa_p = float(_sa_get(spec_augment, "p") or 0.0) if sa_on else 0.0
+        self._cfg = cfg
+        self._handle = ctypes.c_void_p()
+        lib = _lib.load()
+        _lib.check(lib.b200mel_create(ctypes.byref(cfg), dev.index, ctypes.byref(self._handle)))
+        f, c, n = ctypes.c_int32(), ctypes.c_int32(), ctypes.c_int32()
+        _lib.check(lib.b200mel_feature_shape(self._handle, ctypes.byref(f), ctypes.byref(c), ctypes.byref(n)))
+        self.frequency_dim, self.feature_dim, self.fft_length = f.value, c.value, n.value
+        self.audio_feature_type = audio_feature_type
+        self.frame_length, self.frame_step = int(frame_length), int(frame_step)
+        self.spec_augment_enabled = sa_on
+        self.num_freq_masks = cfg.sa_m_F if (cfg.sa_F and cfg.sa_m_F) else 0
+        self.num_time_masks = cfg.sa_m_T if (cfg.sa_T and cfg.sa_p and cfg.sa_m_T) else 0
+
+    # ------------------------------------------------------------------------------------------
+    @classmethod
+    def from_config(cls, config, training: bool = False, device=None) -> "FeatureFrontend":
+        """Build the fused front-end a ``DataConfig`` describes.  SpecAugment is applied only when
+        ``training`` (run/train.py:99-110 applies it to the train split only) and enabled."""
+        sa = config.spec_augment if (training and config.spec_augment.enable) else None
+        return cls(config.audio_feature_type, config.sample_rate, config.frame_length, config.frame_step,
+                   config.fft_length, config.num_mel_bins, config.num_mfcc, config.lower_edge_hertz,
+                   config.upper_edge_hertz, use_delta_accelerate=config.use_delta_accelerate,
+                   spec_augment=sa, device=device)
+
+    def __del__(self):
+        h = getattr(self, "_handle", None)
+        if h is not None and h.value:
+            try:
+                _lib.load().b200mel_destroy(h)
+            except Exception:
+                pass
+            self._handle = ctypes.c_void_p()
+
+    # ------------------------------------------------------------------------------------------
+    def num_frames(self, n_samples: int) -> int:
+        out = ctypes.c_int64()
+        _lib.check(_lib.load().b200mel_num_frames(self._handle, int(n_samples), ctypes.byref(out)))
+        return out.value
+
+    @property
+    def tc_supported(self) -> bool:
+        return bool(_lib.load().b200mel_tc_supported(self._handle))
+
+    @property
+    def launch_count(self) -> int:
+        return int(_lib.load().b200mel_launch_count(self._handle))
+
+    def mel_weights(self) -> np.ndarray:
+        k = self.fft_length // 2 + 1
+        out = np.zeros((k, self._cfg.num_mel_bins), dtype=np.float32)
+        _lib.check(_lib.load().b200mel_mel_weights(self._handle, out.ctypes.data_as(ctypes.c_void_p)))
+        return out
+
+    # ------------------------------------------------------------------------------------------
+    def __call__(self, pcm: torch.Tensor, lengths=None, offsets=None, t_max: Optional[int] = None,
+                 seed: int = 0, first_utterance_id: int = 0, mask_table: Optional[torch.Tensor] = None,
+                 out: Optional[torch.Tensor] = None, kernel: str = "auto", return_status: bool = False
+                 ) -> Tuple[torch.Tensor, torch.Tensor]:
+        """pcm: CUDA int16 or float32; dense [B, L] (``lengths`` optional) or ragged 1-D with
+        ``offsets`` [B] (int64, element offsets) and ``lengths`` [B].  Returns
+        (features [B, t_max, F, C] float32, n_frames [B] int32), both on the device; padding
+        frames are exactly +0.0.  Asynchronous on the current torch stream."""
+        if not pcm.is_cuda or pcm.device != self.device:
+            raise RuntimeError("pcm must live on %s (got %s): there is no CPU path" % (self.device, pcm.device))
+        if pcm.dtype == torch.int16:
+            dt = _lib.PCM_I16
+        elif pcm.dtype == torch.float32:
+            dt = _lib.PCM_F32
+        else:
+            raise ValueError("pcm must be int16 or float32, got %s" % pcm.dtype)
+        pcm = pcm.contiguous()
+        host_lengths = None
+        if offsets is None:
+            if pcm.dim() == 1:
+                pcm = pcm[None]
+            if pcm.dim() != 2:
+                raise ValueError("dense pcm must be [B, L]")
+            B, L = pcm.shape
+            row_stride = L
+            if lengths is None:
+                host_lengths = np.full(B, L, dtype=np.int64)
+        else:
+            if pcm.dim() != 1:
+                raise ValueError("ragged pcm must be 1-D")
+            if lengths is None:
+                raise ValueError("ragged input needs lengths")
+            B, L, row_stride = len(offsets), int(pcm.numel()), 0
+        if lengths is not None and not (isinstance(lengths, torch.Tensor) and lengths.is_cuda):
+            host_lengths = np.asarray(lengths.cpu() if isinstance(lengths, torch.Tensor) else lengths, dtype=np.int64)
+        if host_lengths is not None:
+            if host_lengths.shape != (B,):
+                raise ValueError("lengths must have shape [B]")
+            if host_lengths.size and (host_lengths.min() < 0 or (offsets is None and host_lengths.max() > L)):
+                raise ValueError("lengths outside [0, L]")
+            d_lengths = torch.from_numpy(host_lengths.astype(np.int32)).to(self.device, non_blocking=True)
+        else:
+            d_lengths = lengths.to(torch.int32).contiguous()
+        d_offsets = None
+        if offsets is not None:
+            if isinstance(offsets, torch.Tensor) and offsets.is_cuda:
+                d_offsets = offsets.to(torch.int64).contiguous()
+            else:
+                ho = np.asarray(offsets.cpu() if isinstance(offsets, torch.Tensor) else offsets, dtype=np.int64)
+                if host_lengths is not None and ho.size and (ho.min() < 0 or (ho + host_lengths).max() > L):
+                    raise ValueError("offsets/lengths outside the pcm buffer")
+                d_offsets = torch.from_numpy(ho).to(self.device, non_blocking=True)
+        if t_max is None:
+            if host_lengths is not None:
+                t_max = self.num_frames(int(host_lengths.max())) if B else 0
+            elif offsets is None:
+                t_max = self.num_frames(L)
+            else:
+                raise ValueError("t_max is required when lengths live on the device and pcm is ragged")
+        t_max = int(t_max)
+        F, C = self.frequency_dim, self.feature_dim
+        if out is None:
+            out = torch.empty((B, t_max, F, C), dtype=torch.float32, device=self.device)
+        else:
+            if out.shape != (B, t_max, F, C) or out.dtype != torch.float32 or not out.is_contiguous() \
+                    or out.device != self.device:
+                raise ValueError("out must be a contiguous float32 [B, t_max, F, C] tensor on %s" % self.device)
+        n_frames = torch.empty((B,), dtype=torch.int32, device=self.device)
+        status = torch.zeros((1,), dtype=torch.int32, device=self.device) if return_status else None
+        if mask_table is not None:
+            n = 2 * (self.num_freq_masks + self.num_time_masks)
+            mask_table = mask_table.to(device=self.device, dtype=torch.int32).contiguous()
+            if mask_table.shape != (B, n):
+                raise ValueError("mask_table must be int32 [B, %d]" % n)
+        if kernel not in _lib.KERNELS:
+            raise ValueError("kernel must be one of %s" % sorted(_lib.KERNELS))
+        stream = torch.cuda.current_stream(self.device).cuda_stream
+        _lib.check(_lib.load().b200mel_forward(
+            self._handle, _ptr(pcm), dt, _ptr(d_offsets), _ptr(d_lengths), B, row_stride, _ptr(out), t_max,
+            _ptr(n_frames), _ptr(mask_table), seed & 0xFFFFFFFFFFFFFFFF, first_utterance_id & 0xFFFFFFFFFFFFFFFF,
+            _ptr(status), _lib.KERNELS[kernel], ctypes.c_void_p(stream)))
+        # keep inputs alive until the stream has consumed them
+        for t in (pcm, d_lengths, d_offsets, mask_table):
+            if t is not None:
+                t.record_stream(torch.cuda.current_stream(self.device))
+        if return_status:
+            return out, n_frames, status
+        return out, n_frames
+
+    # ------------------------------------------------------------------------------------------
+    def forward_host(self, pcm, lengths=None, offsets=None, t_max: Optional[int] = None, seed: int = 0,
+                     first_utterance_id: int = 0, out=None, kernel: str = "auto"):
+        """End-to-end call with HOST buffers (numpy arrays or CPU torch tensors; pinned memory gives
+        full PCIe speed): H2D, kernel and D2H are pipelined inside the library and the call returns
+        after the result is in ``out``.  Returns (features, n_frames) as host arrays of the same kind
+        as ``out`` (numpy by default)."""
+        pcm_np = pcm.numpy() if isinstance(pcm, torch.Tensor) else np.asarray(pcm)
+        if pcm_np.dtype == np.int16:
+            dt = _lib.PCM_I16
+        elif pcm_np.dtype == np.float32:
+            dt = _lib.PCM_F32
+        else:
+            raise ValueError("pcm must be int16 or float32")
+        if not pcm_np.flags["C_CONTIGUOUS"]:
+            pcm_np = np.ascontiguousarray(pcm_np)
+        if offsets is None:
+            if pcm_np.ndim == 1:
+                pcm_np = pcm_np[None]
+            B, L = pcm_np.shape
+            row_stride = L
+            lens = np.full(B, L, dtype=np.int32) if lengths is None else np.ascontiguousarray(lengths, dtype=np.int32)
+            offs = None
+        else:
+            B, L, row_stride = len(offsets), pcm_np.size, 0
+            lens = np.ascontiguousarray(lengths, dtype=np.int32)
+            offs = np.ascontiguousarray(offsets, dtype=np.int64)
+        if lens.shape != (B,):
+            raise ValueError("lengths must have shape [B]")
+        if B and (lens.min() < 0 or (offs is None and lens.max() > L)):
+            raise ValueError("lengths outside [0, L]")
+        if t_max is None:
+            t_max = self.num_frames(int(lens.max())) if B else 0
+        F, C = self.frequency_dim, self.feature_dim
+        if out is None:
+            out = np.empty((B, t_max, F, C), dtype=np.float32)
+        out_np = out.numpy() if isinstance(out, torch.Tensor) else out
+        if out_np.shape != (B, t_max, F, C) or out_np.dtype != np.float32 or not out_np.flags["C_CONTIGUOUS"]:
+            raise ValueError("out must be a C-contiguous float32 [B, t_max, F, C] array")
+        n_frames = np.empty((B,), dtype=np.int32)
+        vp = ctypes.c_void_p
+        _lib.check(_lib.load().b200mel_forward_host(
+            self._handle, pcm_np.ctypes.data_as(vp), dt, offs.ctypes.data_as(vp) if offs is not None else None,
+            lens.ctypes.data_as(vp), B, row_stride, pcm_np.size, out_np.ctypes.data_as(vp), int(t_max),
+            n_frames.ctypes.data_as(vp), seed & 0xFFFFFFFFFFFFFFFF, first_utterance_id & 0xFFFFFFFFFFFFFFFF,
+            _lib.KERNELS[kernel]))
+        return out, n_frames
+
+
+# ----------------------------------------------------------------------------------------------
+# stand-alone stages (device tensors)
+# ----------------------------------------------------------------------------------------------
+
+def specaug_draw(num_time: Sequence[int], v: int, F, m_F, T, p, m_T, seed: int, first_utterance_id: int,
+                 device) -> Tuple[torch.Tensor, int, int, torch.Tensor]:
+    """Draw the mask tables of a batch on the device.  Returns (table int32 [B, 2(m_F+m_T)],
+    n_freq_masks, n_time_masks, status int32[1])."""
+    nf = int(m_F) if all([F, m_F]) else 0
+    nt = int(m_T) if all([T, p, m_T]) else 0
+    nt_dev = torch.as_tensor(np.asarray(num_time, dtype=np.int32)).to(device)
+    B = nt_dev.numel()
+    table = torch.zeros((B, 2 * (nf + nt)), dtype=torch.int32, device=device)
+    status = torch.zeros((1,), dtype=torch.int32, device=device)
+    stream = torch.cuda.current_stream(device).cuda_stream
+    _lib.check(_lib.load().b200mel_specaug_draw(
+        _ptr(nt_dev), B, int(v), int(F or 0), int(m_F or 0), int(T or 0), float(p or 0.0), int(m_T or 0),
+        seed & 0xFFFFFFFFFFFFFFFF, first_utterance_id & 0xFFFFFFFFFFFFFFFF, _ptr(table), _ptr(status),
+        ctypes.c_void_p(stream)))
+    return table, nf, nt, status
+
+
+def specaug_apply(feat: torch.Tensor, table: torch.Tensor, n_freq: int, n_time: int) -> torch.Tensor:
+    """feat [B, T, v, C] float32 CUDA -> masked copy."""
+    feat = feat.contiguous()
+    B, T, v, C = feat.shape
+    out = torch.empty_like(feat)
+    stream = torch.cuda.current_stream(feat.device).cuda_stream
+    _lib.check(_lib.load().b200mel_specaug_apply(_ptr(feat), _ptr(out), B, T, v, C, _ptr(table.contiguous()),
+                                                 n_freq, n_time, ctypes.c_void_p(stream)))
+    return out
+
+
+def delta(feat: torch.Tensor, n_frames: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """feat [B, T, v, 1] float32 CUDA -> [B, T, v, 3]."""
+    feat = feat.contiguous()
+    B, T, v, C = feat.shape
+    if C != 1:
+        raise ValueError("delta_accelerate expects a single channel, got %d" % C)
+    out = torch.empty((B, T, v, 3), dtype=torch.float32, device=feat.device)
+    if n_frames is not None:
+        n_frames = n_frames.to(device=feat.device, dtype=torch.int32).contiguous()
+    stream = torch.cuda.current_stream(feat.device).cuda_stream
+    _lib.check(_lib.load().b200mel_delta(_ptr(feat), _ptr(out), _ptr(n_frames), B, T, v, ctypes.c_void_p(stream)))
+    return out
