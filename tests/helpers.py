@@ -24,10 +24,18 @@ REF_MFCC_GRID = [
     (44100, 512, 512, 256, 333, 333, 333, 3333),
 ]
 
-# Stated tolerance (BASELINE.md section 6 / SURVEY 8c):
-LOG_TOL = 1e-3       # max |delta log-mel| where the float64 mel energy >= MEL_FLOOR
+# Stated tolerance (DESIGN.md "Parity tolerance"):
+#   |delta log-mel| <= LOG_TOL where the float64 mel energy >= max(MEL_FLOOR, REL_FLOOR * E_frame),
+#   E_frame = sum of the frame's mel energies; below that floor the bound is linear:
+#   |delta mel| <= LIN_ABS + LIN_REL * mel + REL_LIN * E_frame.
+# REL_FLOOR expresses float32 dynamic range: a float32 FFT (TF's, numpy's or ours) carries an error
+# ~1e-7 * |frame|, so bins > ~80 dB below the frame's energy cannot hold 1e-3 in the log domain
+# (measured: numpy/pocketfft float32 vs float64 on a pure tone = 2.7e-3 without the relative floor,
+# 1.0e-4 with it; the survey measured 0.115 for the same effect).
+LOG_TOL = 1e-3
 MEL_FLOOR = 1e-7
-LIN_ABS, LIN_REL = 1e-9, 1e-3   # below the floor: |delta mel| <= LIN_ABS + LIN_REL * mel
+REL_FLOOR = 1e-8
+LIN_ABS, LIN_REL, REL_LIN = 1e-9, 1e-3, 1e-10
 
 
 def noise_int16(n, seed=0, sigma=0.1):
@@ -61,12 +69,14 @@ def assert_logmel_close(got, want64, eps=1e-12, what=""):
     assert got.shape == want64.shape, (what, got.shape, want64.shape)
     mel_want = np.exp(want64) - eps
     mel_got = np.exp(got) - eps
-    hi = mel_want >= MEL_FLOOR
+    e_frame = np.maximum(mel_want, 0.0).sum(axis=-2 if want64.ndim >= 3 else -1, keepdims=True)
+    hi = mel_want >= np.maximum(MEL_FLOOR, REL_FLOOR * e_frame)
     if hi.any():
         err = np.abs(got - want64)[hi].max()
         assert err <= LOG_TOL, "%s: max |dlog| %.3e > %.1e above the floor" % (what, err, LOG_TOL)
     lo = ~hi
     if lo.any():
-        d = np.abs(mel_got - mel_want)[lo]
-        bound = LIN_ABS + LIN_REL * np.abs(mel_want[lo])
-        assert (d <= bound).all(), "%s: linear-domain error %.3e above bound" % (what, (d - bound).max())
+        d = np.abs(mel_got - mel_want)
+        bound = LIN_ABS + LIN_REL * np.abs(mel_want) + REL_LIN * e_frame
+        assert (d[lo] <= np.broadcast_to(bound, d.shape)[lo]).all(), \
+            "%s: linear-domain error %.3e above bound" % (what, (d - bound)[lo].max())
