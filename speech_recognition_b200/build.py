@@ -30,6 +30,29 @@ def needs_build():
     return any(os.path.getmtime(f) > t for f in sources())
 
 
+def regenerate_tc_tables():
+    """tc_tables_generated.inc (the tensor-core kernel's straight-line mel epilogue) is generated
+    from plan.h by gen_tc_tables.cc; the result is committed, and refreshed here when a host
+    compiler is available and the inputs are newer."""
+    d = os.path.join(HERE, "csrc")
+    out = os.path.join(d, "tc_tables_generated.inc")
+    srcs = [os.path.join(d, "gen_tc_tables.cc"), os.path.join(d, "plan.h")]
+    if os.path.exists(out) and all(os.path.getmtime(out) >= os.path.getmtime(f) for f in srcs):
+        return
+    gxx = shutil.which("g++")
+    if gxx is None:
+        if os.path.exists(out):
+            return
+        raise RuntimeError("g++ not found and tc_tables_generated.inc is missing")
+    exe = os.path.join(HERE, "lib", "gen_tc_tables")
+    os.makedirs(os.path.dirname(exe), exist_ok=True)
+    subprocess.run([gxx, "-O1", "-std=c++17", "-o", exe, srcs[0]], check=True)
+    text = subprocess.run([exe], check=True, capture_output=True, text=True).stdout
+    with open(out, "w") as f:
+        f.write(text)
+    os.remove(exe)
+
+
 def build(force=False, verbose=False):
     if not force and not needs_build():
         return OUT
@@ -39,7 +62,8 @@ def build(force=False, verbose=False):
         "-Xcompiler", "-fPIC", "-shared", "-cudart", "static", "-o", OUT, SRC,
     ]
     if os.path.exists(os.path.join(HERE, "csrc", "tc_kernel.cuh")):
-        cmd += ["-DB200MEL_WITH_TC", "-lcuda"]
+        regenerate_tc_tables()
+        cmd += ["-DB200MEL_WITH_TC"]
     if verbose:
         cmd += ["-Xptxas", "-v"]
     res = subprocess.run(cmd, capture_output=True, text=True)

@@ -176,6 +176,14 @@ int b200mel_create(const b200mel_config* config, int device, b200mel_handle** ou
   }
 #ifdef B200MEL_WITH_TC
   h->tc_ok = tc_plan_build(p, h->tc, h->max_smem_optin);
+  if (h->tc_ok) {
+    // per-device function attribute: set it while this handle's device is current
+    if (cudaFuncSetAttribute(tc_frontend_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmemTotal) != cudaSuccess ||
+        cudaFuncSetAttribute(tc_frontend_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmemTotal) != cudaSuccess) {
+      cudaGetLastError();
+      h->tc_ok = false;
+    }
+  }
 #endif
   *out_handle = h;
   return B200MEL_OK;
@@ -282,6 +290,8 @@ int b200mel_forward(b200mel_handle* h, const void* pcm, int32_t pcm_dtype, const
     return fail(B200MEL_ERR_INVALID_ARGUMENT, "unknown kernel selector");
   if (kernel == B200MEL_KERNEL_TC && !h->tc_ok)
     return fail(B200MEL_ERR_UNSUPPORTED, "the tensor-core kernel does not support this configuration");
+  if (kernel == B200MEL_KERNEL_TC && pcm_dtype != B200MEL_PCM_I16)
+    return fail(B200MEL_ERR_UNSUPPORTED, "the tensor-core kernel takes int16 PCM (its operand split is exact for 16-bit samples)");
   if (batch == 0) return B200MEL_OK;
   if (!lengths || (!pcm) || (t_max > 0 && !out)) return fail(B200MEL_ERR_INVALID_ARGUMENT, "null buffer");
   if (batch > 65535) return fail(B200MEL_ERR_UNSUPPORTED, "batch > 65535: split the call");
@@ -311,7 +321,7 @@ int b200mel_forward(b200mel_handle* h, const void* pcm, int32_t pcm_dtype, const
     if (!n_frames) return B200MEL_OK;
   }
 #ifdef B200MEL_WITH_TC
-  if (h->tc_ok && kernel != B200MEL_KERNEL_GENERIC && t_max > 0) {
+  if (h->tc_ok && kernel != B200MEL_KERNEL_GENERIC && t_max > 0 && pcm_dtype == B200MEL_PCM_I16) {
     int rc = tc_launch(h->tc, kp, h->sm_count, st);
     if (rc != 0) return cuda_fail(cudaGetLastError(), "tc_frontend_kernel launch");
     h->launches.fetch_add(1);

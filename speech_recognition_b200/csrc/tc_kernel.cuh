@@ -1,0 +1,116 @@
+// tc_kernel.cuh - tensor-core (tcgen05) front-end kernel for the shipped parameter set
+// (frame_length 320, frame_step 160, fft_length 320, 80 mel bins: libri / kspon / clovacall YAMLs).
+//
+// Why tensor cores: ncu on the generic kernel shows the path is issue-bound on the CUDA cores at
+// 3 % DRAM throughput (profiles/r1a_generic_kernel.md); a 320-point FFT + mel + log is ~15 flop/B,
+// above the FP32 ridge, so the DFT has to leave the FP32 pipe to approach the HBM roofline.
+//
+// Math.  n = 5 j + r (r = 0..4, j = 0..63), k = k1 + 64 k2:
+//     X[k1 + 64 k2] = sum_r W5^{r k2} * Y_r[k1],   Y_r[k1] = sum_j s[5 j + r] * (w[5 j + r] W320^{(5 j + r) k1})
+//   * Y_r (five 64-point "windowed, pre-twiddled" DFTs of the decimated sample streams) is a GEMM
+//     [128 frames x 64] x [64 x 64] per residue on tcgen05.mma, accumulators in TMEM.
+//       - A operand: the int16 PCM itself, split EXACTLY into two f16 terms (hi = rn_f16(x),
+//         lo = x - hi), de-interleaved by 5 into contiguous streams y_r[e] = s[5 e + r] in shared
+//         memory.  Frame t needs y_r[32 t .. 32 t + 63]: consecutive frames overlap by half a row,
+//         so the A tile is a *Hankel view* of the stream - a K-major SWIZZLE_64B descriptor whose
+//         row pitch (64 B) is half the row length (128 B).  Nothing is materialised twice.
+//       - B operand: window x twiddle matrix in two f16 terms (22 bits), K-major SWIZZLE_128B.
+//       - three passes per residue (lo*Bhi, hi*Blo, hi*Bhi) accumulate into one f32 accumulator:
+//         float32-class accuracy (the dropped lo*Blo term is < 2^-22 relative per sample).
+//   * the radix-5 stage over r, power, sparse mel (FFMA immediates), log and the SpecAugment /
+//     delta / padding epilogue run on the CUDA cores, one thread per frame, straight from TMEM.
+//
+// Roles (288 threads, one persistent CTA per SM): warps 0-3 epilogue (thread = frame = TMEM lane),
+// warps 4-7 producers (PCM -> f16 hi/lo streams), warp 8 MMA issuer.  TMEM is used as a ring of
+// eight 64-column accumulator slots (a tile needs five), shared memory holds B (80 KB), one A stage
+// (85 KB) and the output staging tile (42 KB).
+#pragma once
+
+#include <vector>
+
+#include "common.cuh"
+#include "plan.h"
+#include "tc_ptx.cuh"
+#include "tc_tables_generated.inc"
+
+namespace b200mel {
+
+constexpr int kTcTileM = 128;              // frames per tile
+constexpr int kTcStreamBytes = 8704;       // 136 rows x 64 B (129 needed), multiple of 512
+constexpr int kTcBBytes = 8192;            // one 64 x 64 f16 matrix
+constexpr int kTcSmemB = 0;
+constexpr int kTcSmemA = 10 * kTcBBytes;                       // 81920
+constexpr int kTcSmemOut = kTcSmemA + 10 * kTcStreamBytes;     // 168960
+constexpr int kTcOutPitch = 84;                                // floats per staged row (16-B aligned, conflict-free)
+constexpr int kTcSmemCtl = kTcSmemOut + kTcTileM * kTcOutPitch * 4;  // 211968
+constexpr int kTcSmemTotal = kTcSmemCtl + 256 + 1024;          // + control block + alignment slack
+constexpr int kTcThreads = 288;
+constexpr int kTcBScaleLog2 = 10;          // B is stored as 2^10 * w * twiddle
+// power = |Y|^2 * 2^(-2*10) (B scale) * 2^(-30) (int16 -> [-1, 1) twice)
+#define TC_PSCALE 0x1p-50f
+
+struct TcPlan {
+  uint8_t* d_b = nullptr;   // 10 x 8 KB swizzled shared-memory image of the B matrices
+  float log_eps = 0.0f;     // logf(epsilon): the exact value for all-zero mel energies (silence)
+};
+
+// Host: does this plan equal the parameter set the epilogue was generated for?
+inline bool tc_plan_matches(const HostPlan& p) {
+  const b200mel_config& c = p.cfg;
+  if (c.audio_feature_type != B200MEL_FEATURE_LOG_MEL) return false;
+  if (c.frame_length != 320 || c.frame_step != 160 || p.N != 320 || c.num_mel_bins != TC_MEL_BINS) return false;
+  if (static_cast<int>(p.mel_w.size()) != TC_MEL_NNZ) return false;
+  for (int m = 0; m < TC_MEL_BINS; ++m)
+    if (p.mel_start[m] != kTcMelStart[m] || p.mel_count[m] != kTcMelCount[m]) return false;
+  for (int i = 0; i < TC_MEL_NNZ; ++i) {
+    unsigned u;
+    std::memcpy(&u, &p.mel_w[i], 4);
+    if (u != kTcMelWBits[i]) return false;
+  }
+  return true;
+}
+
+// Host: build the B operand (window x twiddle, two f16 terms) directly in its swizzled shared-memory
+// layout: matrix (term, r) at (term*5 + r) * 8 KB; row n (output column) = 128 B of K = 64 f16;
+// SWIZZLE_128B: 16-byte chunk index ^= (row & 7).
+//   column 0: k1 = 0 (real);  column 1: the k1 = 32 term, sum_j (-1)^j s w (real, phase e^{-i pi r/5}
+//   applied in the epilogue);  columns 2 k1, 2 k1 + 1: Re / Im of w W320^{(5j+r) k1}, k1 = 1..31.
+inline bool tc_plan_build(const HostPlan& p, TcPlan& tc, int max_smem_optin) {
+  if (!tc_plan_matches(p) || max_smem_optin < kTcSmemTotal) return false;
+  std::vector<__half> img(10 * kTcBBytes / 2);
+  const double scale = static_cast<double>(1 << kTcBScaleLog2);
+  for (int r = 0; r < 5; ++r)
+    for (int n = 0; n < 64; ++n)
+      for (int j = 0; j < 64; ++j) {
+        const int s = 5 * j + r;
+        const double w = static_cast<double>(p.window[s]);
+        double f;
+        if (n == 0) f = 1.0;
+        else if (n == 1) f = (j & 1) ? -1.0 : 1.0;
+        else {
+          const int k1 = n >> 1;
+          const double a = -2.0 * M_PI * static_cast<double>((s * k1) % 320) / 320.0;
+          f = (n & 1) ? sin(a) : cos(a);
+        }
+        const double v = scale * w * f;
+        const __half hi = __float2half_rn(static_cast<float>(v));
+        const __half lo = __float2half_rn(static_cast<float>(v - static_cast<double>(__half2float(hi))));
+        const uint32_t o = 128 * n + 2 * j;
+        const uint32_t ph = o ^ (((o >> 7) & 7) << 4);
+        img[((0 * 5 + r) * kTcBBytes + ph) / 2] = hi;
+        img[((1 * 5 + r) * kTcBBytes + ph) / 2] = lo;
+      }
+  if (cudaMalloc(reinterpret_cast<void**>(&tc.d_b), 10 * kTcBBytes) != cudaSuccess) return false;
+  if (cudaMemcpy(tc.d_b, img.data(), 10 * kTcBBytes, cudaMemcpyHostToDevice) != cudaSuccess) return false;
+  tc.log_eps = logf(p.cfg.epsilon);
+  return true;
+}
+
+inline void tc_plan_free(TcPlan& tc) {
+  cudaFree(tc.d_b);
+  tc.d_b = nullptr;
+}
+
+}  // namespace b200mel
+
+#include "tc_kernel_device.cuh"
