@@ -16,19 +16,8 @@ struct TcParams {
 // producer: 40 consecutive int16 samples -> 8 consecutive elements of each of the 5 decimated
 // streams, as exact f16 (hi, lo) pairs.
 // ---------------------------------------------------------------------------------------------
-__device__ __forceinline__ uint4 tc_load8(const short* __restrict__ base, int64_t s, int32_t len, bool aligned) {
-  // 8 samples starting at utterance-relative index s (multiple of 8); zero outside [0, len)
-  if (s >= 0 && s + 8 <= len) {
-    if (aligned) return __ldg(reinterpret_cast<const uint4*>(base + s));
-    uint32_t w[4];
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      uint32_t lo = static_cast<uint16_t>(__ldg(base + s + 2 * i));
-      uint32_t hi = static_cast<uint16_t>(__ldg(base + s + 2 * i + 1));
-      w[i] = lo | (hi << 16);
-    }
-    return make_uint4(w[0], w[1], w[2], w[3]);
-  }
+__device__ __noinline__ uint4 tc_load8_slow(const short* __restrict__ base, int64_t s, int32_t len) {
+  // unaligned utterance start, or a chunk that crosses [0, len): element-wise, zero outside
   uint32_t w[4];
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
@@ -38,6 +27,11 @@ __device__ __forceinline__ uint4 tc_load8(const short* __restrict__ base, int64_
     w[i] = lo | (hi << 16);
   }
   return make_uint4(w[0], w[1], w[2], w[3]);
+}
+// 8 samples starting at utterance-relative index s (a multiple of 8); zero outside [0, len)
+__device__ __forceinline__ uint4 tc_load8(const short* __restrict__ base, int64_t s, int32_t len, bool aligned) {
+  if (aligned && s >= 0 && s + 8 <= len) return __ldg(reinterpret_cast<const uint4*>(base + s));
+  return tc_load8_slow(base, s, len);
 }
 
 // x = 256 h + l (h = signed high byte, l = unsigned low byte).  With the f16 "magic" encodings
@@ -60,7 +54,9 @@ __device__ __forceinline__ void tc_split_pair(uint32_t d, uint32_t& hi_out, uint
 }
 
 // One group: raw[5] = 40 samples -> 10 x 16-byte stores (stream (term, r), element block g).
-__device__ __forceinline__ void tc_produce_group(const uint4* raw, uint8_t* sA, int g) {
+// Out of line on purpose: three call sites share one copy of the code (instruction-cache footprint).
+__device__ __noinline__ void tc_produce_group(uint4 r0, uint4 r1, uint4 r2, uint4 r3, uint4 r4, uint8_t* sA, int g) {
+  const uint4 raw[5] = {r0, r1, r2, r3, r4};
   uint32_t w[20];
 #pragma unroll
   for (int q = 0; q < 5; ++q) {

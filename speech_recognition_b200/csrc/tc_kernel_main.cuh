@@ -14,7 +14,10 @@ struct TcCtl {
 
 // log(mel + eps); exactly log(eps) for silence (the reference's golden fixture pins that value)
 __device__ __forceinline__ float tc_finish(float acc, float eps, float log_eps) {
-  return acc == 0.0f ? log_eps : __logf(acc + eps);
+  // mel + eps >= 1e-12 is a normal float: one MUFU.LG2 + one FMUL (abs error ~ 2^-22 * |log|)
+  float l2;
+  asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(l2) : "f"(acc + eps));
+  return acc == 0.0f ? log_eps : l2 * 0.69314718055994530942f;
 }
 
 #define TC_FINISH4(G, A, B, C, D)                                                              \
@@ -22,22 +25,11 @@ __device__ __forceinline__ float tc_finish(float acc, float eps, float log_eps) 
       make_float4(tc_finish(A, eps, log_eps), tc_finish(B, eps, log_eps), tc_finish(C, eps, log_eps), \
                   tc_finish(D, eps, log_eps))
 
-// one k1 in 1..31: columns (COL, COL+1) of the five residue accumulators of this chunk
-#define TC_STEP(K1, COL)                                                             \
-  {                                                                                  \
-    float xr[5], xi[5], p0, p1, p2, p3, p4;                                          \
-    _Pragma("unroll") for (int r = 0; r < 5; ++r) {                                  \
-      xr[r] = d[r][COL];                                                             \
-      xi[r] = d[r][(COL) + 1];                                                       \
-    }                                                                                \
-    tc_radix5_power(xr, xi, p0, p1, p2, p3, p4);                                     \
-    TC_MEL_K1_##K1(p0, p1, p2, p3, p4);                                              \
-  }
-
 template <int C>
 __global__ void __launch_bounds__(kTcThreads, 1) tc_frontend_kernel(const KernelParams p, const TcParams tp) {
   extern __shared__ __align__(1024) uint8_t tc_smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(tc_smem_raw) + 1023) & ~uintptr_t(1023));
+  // 1024-byte alignment (swizzle atoms) without losing the shared address space of the pointer
+  uint8_t* smem = tc_smem_raw + ((1024u - (tc::smem_u32(tc_smem_raw) & 1023u)) & 1023u);
   uint8_t* sB = smem + kTcSmemB;
   uint8_t* sA = smem + kTcSmemA;
   float* sOut = reinterpret_cast<float*>(smem + kTcSmemOut);
@@ -68,7 +60,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_frontend_kernel(const Kernel
   bool timed_out = false;
 
   if (warp >= 4 && warp < 8) {
-    // ======================= PRODUCERS ==========================================================
+    // ======================= PRODUCERS (4 warps) ================================================
     const int ptid = tid - 128;
     uint32_t n = 0;  // active tiles processed so far by this CTA
     for (int tile = blockIdx.x; tile < tp.total_tiles; tile += gridDim.x) {
@@ -80,15 +72,23 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_frontend_kernel(const Kernel
       const short* pcm = reinterpret_cast<const short*>(p.pcm) + base;
       const bool aligned = (reinterpret_cast<uintptr_t>(pcm) & 15) == 0;
       const int64_t s_begin = 160 * (static_cast<int64_t>(j) * tp.tout - tp.halo);
-      if (n > 0 && !tc::mbar_wait(&ctl->a_empty, (n - 1) & 1)) timed_out = true;
-      // 516 groups of 40 samples = 129 hops: the 128 frames of the tile + the half-row of overlap
-      for (int g = ptid; g < 516; g += 128) {
-        uint4 raw[5];
-        const int64_t s0 = s_begin + 40 * g;
+      // 516 groups of 40 samples = 129 hops (128 frames + the half-row of overlap): four per thread,
+      // the last four by threads 0..3.  All global loads are issued before the wait below, so the
+      // DRAM latency overlaps the MMAs that are still reading the previous tile's streams.
+      uint4 raw[4][5], rawt[5];
 #pragma unroll
-        for (int q = 0; q < 5; ++q) raw[q] = tc_load8(pcm, s0 + 8 * q, len, aligned);
-        tc_produce_group(raw, sA, g);
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int q = 0; q < 5; ++q) raw[i][q] = tc_load8(pcm, s_begin + 40 * (ptid + 128 * i) + 8 * q, len, aligned);
+      if (ptid < 4) {
+#pragma unroll
+        for (int q = 0; q < 5; ++q) rawt[q] = tc_load8(pcm, s_begin + 40 * (ptid + 512) + 8 * q, len, aligned);
       }
+      if (n > 0 && !timed_out && !tc::mbar_wait(&ctl->a_empty, (n - 1) & 1)) timed_out = true;
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+        tc_produce_group(raw[i][0], raw[i][1], raw[i][2], raw[i][3], raw[i][4], sA, ptid + 128 * i);
+      if (ptid < 4) tc_produce_group(rawt[0], rawt[1], rawt[2], rawt[3], rawt[4], sA, ptid + 512);
       tc::fence_async_smem();  // generic-proxy writes -> visible to the tensor core (async proxy)
       tc::mbar_arrive(&ctl->a_full);
       ++n;
@@ -103,14 +103,14 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_frontend_kernel(const Kernel
       const int b = tile / tp.tiles_per_utt, j = tile - b * tp.tiles_per_utt;
       const int n_fr = frames_of(p.lengths[b], 320, 160);
       if (j * tp.tout >= n_fr) continue;
-      if (!tc::mbar_wait(&ctl->a_full, n & 1)) timed_out = true;
+      if (!timed_out && !tc::mbar_wait(&ctl->a_full, n & 1)) timed_out = true;
       tc::tc_fence_after();
       if (lane == 0) {
-#pragma unroll
+#pragma unroll 1
         for (int r = 0; r < 5; ++r) {
           // slots of residues 3, 4 were residues 0, 1 of the previous tile: wait for its epilogue
           if (r == 3 && n > 0) {
-            if (!tc::mbar_wait(&ctl->acc_empty, (n - 1) & 1)) timed_out = true;
+            if (!timed_out && !tc::mbar_wait(&ctl->acc_empty, (n - 1) & 1)) timed_out = true;
             tc::tc_fence_after();
           }
           const uint32_t d_tmem = tmem_base + (((5u * n + r) & 7u) << 6);
@@ -158,20 +158,23 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_frontend_kernel(const Kernel
         }
       }
       if (active) {
-        if (!tc::mbar_wait(&ctl->acc_full, n & 1)) timed_out = true;
+        if (!timed_out && !tc::mbar_wait(&ctl->acc_full, n & 1)) timed_out = true;
         tc::tc_fence_after();
         TC_DECL_ACC
-        float d[5][16];
-        // ---- chunk 0: k1 = 0 (col 0), the k1 = 32 term (col 1), k1 = 1..7 ----
-#pragma unroll
-        for (int r = 0; r < 5; ++r) tc::tmem_ld16(tmem_base + lane_base + (((5u * n + r) & 7u) << 6) + 0, d[r]);
+        // 8 chunks of 8 accumulator columns (4 values of k1) per residue.  The butterfly code is one
+        // rolled loop body; only the mel FFMAs (immediates, named accumulators) are per-chunk code,
+        // selected by a warp-uniform switch - the whole epilogue stays inside the instruction cache.
+        float Q[6], P[20], d[5][8];
+#define TC_LOAD(COL)                                                                                     \
+  _Pragma("unroll") for (int r = 0; r < 5; ++r)                                                          \
+      tc::tmem_ld8(tmem_base + lane_base + (((5u * n + r) & 7u) << 6) + (COL), d[r]);
+        TC_LOAD(0)
         tc::tmem_ld_wait();
         {
-          float x[5], p0, p1, p2;
+          float x[5];
 #pragma unroll
           for (int r = 0; r < 5; ++r) x[r] = d[r][0];
-          tc_radix5_power_real(x, p0, p1, p2);
-          TC_MEL_K1_0(p0, p1, p2);
+          tc_radix5_power_real(x, Q[0], Q[1], Q[2]);
         }
         {
           // Y_r[32] = R_r * e^{-i pi r / 5}
@@ -179,34 +182,55 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_frontend_kernel(const Kernel
                                -0.80901699437494742410f};
           const float sr[5] = {0.0f, 0.58778525229247312917f, 0.95105651629515357212f, 0.95105651629515357212f,
                                0.58778525229247312917f};
-          float xr[5], xi[5], p0, p1, p2, p3, p4;
+          float xr[5], xi[5], p3, p4;
 #pragma unroll
           for (int r = 0; r < 5; ++r) {
             xr[r] = d[r][1] * cr[r];
             xi[r] = -d[r][1] * sr[r];
           }
-          tc_radix5_power(xr, xi, p0, p1, p2, p3, p4);
-          TC_MEL_K1_32(p0, p1, p2);
+          tc_radix5_power(xr, xi, Q[3], Q[4], Q[5], p3, p4);
         }
-        TC_STEP(1, 2) TC_STEP(2, 4) TC_STEP(3, 6) TC_STEP(4, 8) TC_STEP(5, 10) TC_STEP(6, 12) TC_STEP(7, 14)
-        // ---- chunk 1: k1 = 8..15 ----
 #pragma unroll
-        for (int r = 0; r < 5; ++r) tc::tmem_ld16(tmem_base + lane_base + (((5u * n + r) & 7u) << 6) + 16, d[r]);
-        tc::tmem_ld_wait();
-        TC_STEP(8, 0) TC_STEP(9, 2) TC_STEP(10, 4) TC_STEP(11, 6) TC_STEP(12, 8) TC_STEP(13, 10) TC_STEP(14, 12) TC_STEP(15, 14)
-        // ---- chunk 2: k1 = 16..23 ----
+        for (int s = 1; s < 4; ++s) {
+          float xr[5], xi[5];
 #pragma unroll
-        for (int r = 0; r < 5; ++r) tc::tmem_ld16(tmem_base + lane_base + (((5u * n + r) & 7u) << 6) + 32, d[r]);
-        tc::tmem_ld_wait();
-        TC_STEP(16, 0) TC_STEP(17, 2) TC_STEP(18, 4) TC_STEP(19, 6) TC_STEP(20, 8) TC_STEP(21, 10) TC_STEP(22, 12) TC_STEP(23, 14)
-        // ---- chunk 3: k1 = 24..31 ----
+          for (int r = 0; r < 5; ++r) {
+            xr[r] = d[r][2 * s];
+            xi[r] = d[r][2 * s + 1];
+          }
+          tc_radix5_power(xr, xi, P[5 * s], P[5 * s + 1], P[5 * s + 2], P[5 * s + 3], P[5 * s + 4]);
+        }
+        TC_MEL_CHUNK_0(Q, P);
+#pragma unroll 1
+        for (int c = 1; c < 8; ++c) {
+          TC_LOAD(8 * c)
+          tc::tmem_ld_wait();
+          if (c == 7) {
+            // all TMEM reads of this tile are done: hand the slots back before the remaining arithmetic
+            tc::tc_fence_before();
+            tc::mbar_arrive(&ctl->acc_empty);
+          }
 #pragma unroll
-        for (int r = 0; r < 5; ++r) tc::tmem_ld16(tmem_base + lane_base + (((5u * n + r) & 7u) << 6) + 48, d[r]);
-        tc::tmem_ld_wait();
-        // all TMEM reads of this tile are done: hand the slots back before the remaining arithmetic
-        tc::tc_fence_before();
-        tc::mbar_arrive(&ctl->acc_empty);
-        TC_STEP(24, 0) TC_STEP(25, 2) TC_STEP(26, 4) TC_STEP(27, 6) TC_STEP(28, 8) TC_STEP(29, 10) TC_STEP(30, 12) TC_STEP(31, 14)
+          for (int s = 0; s < 4; ++s) {
+            float xr[5], xi[5];
+#pragma unroll
+            for (int r = 0; r < 5; ++r) {
+              xr[r] = d[r][2 * s];
+              xi[r] = d[r][2 * s + 1];
+            }
+            tc_radix5_power(xr, xi, P[5 * s], P[5 * s + 1], P[5 * s + 2], P[5 * s + 3], P[5 * s + 4]);
+          }
+          switch (c) {
+            case 1: TC_MEL_CHUNK_1(Q, P); break;
+            case 2: TC_MEL_CHUNK_2(Q, P); break;
+            case 3: TC_MEL_CHUNK_3(Q, P); break;
+            case 4: TC_MEL_CHUNK_4(Q, P); break;
+            case 5: TC_MEL_CHUNK_5(Q, P); break;
+            case 6: TC_MEL_CHUNK_6(Q, P); break;
+            default: TC_MEL_CHUNK_7(Q, P); break;
+          }
+        }
+#undef TC_LOAD
         TC_MEL_TAIL;
         ++n;
       }
