@@ -19,6 +19,21 @@ __global__ void specaug_draw_kernel(const int32_t* __restrict__ num_time, int ba
   if (bad && status) atomicOr(status, 1);
 }
 
+// Same draws from the sample counts (num_time = frames_of(lengths[b])): the pre-pass of the fused
+// tensor-core kernel when the caller passes no mask table.
+__global__ void specaug_draw_from_lengths_kernel(const int32_t* __restrict__ lengths, int batch, int Lw, int H, int v,
+                                                 int F, int m_F, int T, float p, int m_T, uint64_t seed,
+                                                 uint64_t first_utt, int32_t* __restrict__ table, int32_t* status) {
+  int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= batch) return;
+  int32_t local[2 * kMaxMasks];
+  int bad = specaug_draw_table(frames_of(lengths[b], Lw, H), v, F, m_F, T, p, m_T, seed,
+                               first_utt + static_cast<uint64_t>(b), local);
+  int n = 2 * (m_F + m_T);
+  for (int i = 0; i < n; ++i) table[static_cast<size_t>(b) * n + i] = local[i];
+  if (bad && status) atomicOr(status, 1);
+}
+
 // audio *= mask (data.py:286-288, 299-301) over [B, t_max, v, C].
 __global__ void specaug_apply_kernel(const float* __restrict__ in, float* __restrict__ out, int64_t t_max, int v,
                                      int C, const int32_t* __restrict__ table, int m_F, int m_T) {

@@ -321,8 +321,26 @@ int b200mel_forward(b200mel_handle* h, const void* pcm, int32_t pcm_dtype, const
     if (!n_frames) return B200MEL_OK;
   }
 #ifdef B200MEL_WITH_TC
-  if (h->tc_ok && kernel != B200MEL_KERNEL_GENERIC && t_max > 0 && pcm_dtype == B200MEL_PCM_I16) {
+  // the tensor-core kernel stores rows with 16-byte bulk copies / float4
+  const bool tc_aligned = (reinterpret_cast<uintptr_t>(out) & 15) == 0;
+  if (kernel == B200MEL_KERNEL_TC && !tc_aligned)
+    return fail(B200MEL_ERR_INVALID_ARGUMENT, "the tensor-core kernel needs a 16-byte aligned output buffer");
+  if (h->tc_ok && kernel != B200MEL_KERNEL_GENERIC && t_max > 0 && pcm_dtype == B200MEL_PCM_I16 && tc_aligned) {
+    const int n_masks = kp.n_masks_f + kp.n_masks_t;
+    int32_t* tmp_table = nullptr;
+    if (n_masks > 0 && !mask_table) {
+      // pre-pass: the utterances' mask tables (same Philox stream as b200mel_specaug_draw), in a
+      // stream-ordered scratch buffer so that concurrent callers of one handle do not share state
+      CU_CHECK(cudaMallocAsync(reinterpret_cast<void**>(&tmp_table),
+                               static_cast<size_t>(batch) * 2 * n_masks * sizeof(int32_t), st));
+      specaug_draw_from_lengths_kernel<<<(batch + 127) / 128, 128, 0, st>>>(
+          lengths, batch, kp.Lw, kp.H, kp.F, kp.sa_F, kp.n_masks_f, kp.sa_T, kp.sa_p, kp.n_masks_t, seed,
+          first_utterance_id, tmp_table, status);
+      kp.mask_table = tmp_table;
+      h->launches.fetch_add(1);
+    }
     int rc = tc_launch(h->tc, kp, h->sm_count, st);
+    if (tmp_table) cudaFreeAsync(tmp_table, st);
     if (rc != 0) return cuda_fail(cudaGetLastError(), "tc_frontend_kernel launch");
     h->launches.fetch_add(1);
     return B200MEL_OK;

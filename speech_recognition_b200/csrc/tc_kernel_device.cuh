@@ -28,12 +28,6 @@ __device__ __noinline__ uint4 tc_load8_slow(const short* __restrict__ base, int6
   }
   return make_uint4(w[0], w[1], w[2], w[3]);
 }
-// 8 samples starting at utterance-relative index s (a multiple of 8); zero outside [0, len)
-__device__ __forceinline__ uint4 tc_load8(const short* __restrict__ base, int64_t s, int32_t len, bool aligned) {
-  if (aligned && s >= 0 && s + 8 <= len) return __ldg(reinterpret_cast<const uint4*>(base + s));
-  return tc_load8_slow(base, s, len);
-}
-
 // x = 256 h + l (h = signed high byte, l = unsigned low byte).  With the f16 "magic" encodings
 // 0x64uu = 1024 + uu:  hq = (1024 + (h + 128)) - 1156 = h - 4,  lq = 1024 + l, so that
 //   hi = fma(hq, 256, lq) = rn_f16(x)         (one rounding)

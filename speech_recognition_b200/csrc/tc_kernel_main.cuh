@@ -9,7 +9,6 @@ struct TcCtl {
   uint64_t acc_full;   // tcgen05.commit -> epilogue: the 5 accumulators of this tile are complete
   uint64_t acc_empty;  // epilogue (128 arrivals) -> MMA: this tile's TMEM slots may be overwritten
   uint32_t tmem_base;
-  int32_t table[2 * kMaxMasks];
 };
 
 // log(mel + eps); exactly log(eps) for silence (the reference's golden fixture pins that value)
@@ -24,6 +23,45 @@ __device__ __forceinline__ float tc_finish(float acc, float eps, float log_eps) 
   *reinterpret_cast<float4*>(out_row + 4 * (G)) =                                              \
       make_float4(tc_finish(A, eps, log_eps), tc_finish(B, eps, log_eps), tc_finish(C, eps, log_eps), \
                   tc_finish(D, eps, log_eps))
+
+// SpecAugment on the thread's own staged row (data.py:286-288, 299-301): audio *= mask, so a masked
+// negative value becomes -0.0 exactly like the reference's multiply.  tb = (start, width) pairs,
+// frequency masks first.  Out of line: it runs once per tile and must not bloat the hot loop.
+__device__ __noinline__ void tc_mask_row(float* row, const int32_t* __restrict__ tb, int n_f, int n_t, int t) {
+  bool tm = false;
+  for (int i = 0; i < n_t; ++i) {
+    const int s = __ldg(tb + 2 * (n_f + i)), w = __ldg(tb + 2 * (n_f + i) + 1);
+    tm = tm || (t >= s && t < s + w);
+  }
+  if (tm) {
+    for (int g = 0; g < 20; ++g) {
+      float4 v = *reinterpret_cast<float4*>(row + 4 * g);
+      v.x *= 0.0f; v.y *= 0.0f; v.z *= 0.0f; v.w *= 0.0f;
+      *reinterpret_cast<float4*>(row + 4 * g) = v;
+    }
+  }
+  for (int i = 0; i < n_f; ++i) {
+    const int s = __ldg(tb + 2 * i), w = __ldg(tb + 2 * i + 1);
+    const int e = s + w < 80 ? s + w : 80;
+    for (int m = s > 0 ? s : 0; m < e; ++m) row[m] *= 0.0f;
+  }
+}
+
+__device__ __noinline__ void tc_zero_row(float* row) {
+  for (int g = 0; g < 20; ++g) *reinterpret_cast<float4*>(row + 4 * g) = make_float4(0.f, 0.f, 0.f, 0.f);
+}
+
+// Unaligned utterance start (ragged offsets that are not a multiple of 8 samples): element-wise
+// producer, one group at a time.  Rare path, kept out of line.
+__device__ __noinline__ void tc_produce_tile_slow(const short* __restrict__ pcm, int64_t s_begin, int32_t len,
+                                                  uint8_t* sA, int ptid) {
+  for (int g = ptid; g < 516; g += 128) {
+    uint4 raw[5];
+#pragma unroll
+    for (int q = 0; q < 5; ++q) raw[q] = tc_load8_slow(pcm, s_begin + 40 * g + 8 * q, len);
+    tc_produce_group(raw[0], raw[1], raw[2], raw[3], raw[4], sA, g);
+  }
+}
 
 template <int C>
 __global__ void __launch_bounds__(kTcThreads, 1) tc_frontend_kernel(const KernelParams p, const TcParams tp) {
@@ -70,25 +108,40 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_frontend_kernel(const Kernel
       if (j * tp.tout >= n_fr) continue;  // nothing but padding: the epilogue zero-fills
       const int64_t base = p.offsets ? p.offsets[b] : static_cast<int64_t>(b) * p.row_stride;
       const short* pcm = reinterpret_cast<const short*>(p.pcm) + base;
-      const bool aligned = (reinterpret_cast<uintptr_t>(pcm) & 15) == 0;
-      const int64_t s_begin = 160 * (static_cast<int64_t>(j) * tp.tout - tp.halo);
-      // 516 groups of 40 samples = 129 hops (128 frames + the half-row of overlap): four per thread,
-      // the last four by threads 0..3.  All global loads are issued before the wait below, so the
-      // DRAM latency overlaps the MMAs that are still reading the previous tile's streams.
-      uint4 raw[4][5], rawt[5];
+      const int32_t s_begin = 160 * (j * tp.tout - tp.halo);
+      if ((reinterpret_cast<uintptr_t>(pcm) & 15) == 0) {
+        // 516 groups of 40 samples = 129 hops (128 frames + the half-row of overlap): four per thread,
+        // the last four by threads 0..3.  All global loads are issued before the wait below, so the
+        // DRAM latency overlaps the MMAs that are still reading the previous tile's streams.
+        // Every frame t < n_fr ends at a multiple of 8 samples <= len, so clamping the 8-sample
+        // block index into [0, len/8 - 1] never changes a sample a valid frame uses; blocks outside
+        // only feed rows that the epilogue zero-fills (t >= n_fr) or drops (t < 0).
+        const uint4* src = reinterpret_cast<const uint4*>(pcm);
+        const int32_t blk_max = (len >> 3) - 1;  // n_fr >= 1 here, so len >= 320
+        uint4 raw[4][5], rawt[5];
 #pragma unroll
-      for (int i = 0; i < 4; ++i)
+        for (int i = 0; i < 4; ++i)
 #pragma unroll
-        for (int q = 0; q < 5; ++q) raw[i][q] = tc_load8(pcm, s_begin + 40 * (ptid + 128 * i) + 8 * q, len, aligned);
-      if (ptid < 4) {
+          for (int q = 0; q < 5; ++q) {
+            const int32_t blk = (s_begin >> 3) + 5 * (ptid + 128 * i) + q;
+            raw[i][q] = __ldg(src + min(max(blk, 0), blk_max));
+          }
+        if (ptid < 4) {
 #pragma unroll
-        for (int q = 0; q < 5; ++q) rawt[q] = tc_load8(pcm, s_begin + 40 * (ptid + 512) + 8 * q, len, aligned);
+          for (int q = 0; q < 5; ++q) {
+            const int32_t blk = (s_begin >> 3) + 5 * (ptid + 512) + q;
+            rawt[q] = __ldg(src + min(max(blk, 0), blk_max));
+          }
+        }
+        if (n > 0 && !timed_out && !tc::mbar_wait(&ctl->a_empty, (n - 1) & 1)) timed_out = true;
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+          tc_produce_group(raw[i][0], raw[i][1], raw[i][2], raw[i][3], raw[i][4], sA, ptid + 128 * i);
+        if (ptid < 4) tc_produce_group(rawt[0], rawt[1], rawt[2], rawt[3], rawt[4], sA, ptid + 512);
+      } else {
+        if (n > 0 && !timed_out && !tc::mbar_wait(&ctl->a_empty, (n - 1) & 1)) timed_out = true;
+        tc_produce_tile_slow(pcm, s_begin, len, sA, ptid);
       }
-      if (n > 0 && !timed_out && !tc::mbar_wait(&ctl->a_empty, (n - 1) & 1)) timed_out = true;
-#pragma unroll
-      for (int i = 0; i < 4; ++i)
-        tc_produce_group(raw[i][0], raw[i][1], raw[i][2], raw[i][3], raw[i][4], sA, ptid + 128 * i);
-      if (ptid < 4) tc_produce_group(rawt[0], rawt[1], rawt[2], rawt[3], rawt[4], sA, ptid + 512);
       tc::fence_async_smem();  // generic-proxy writes -> visible to the tensor core (async proxy)
       tc::mbar_arrive(&ctl->a_full);
       ++n;
@@ -138,24 +191,22 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_frontend_kernel(const Kernel
     const float eps = p.epsilon, log_eps = tp.log_eps;
     const int n_masks = p.n_masks_f + p.n_masks_t;
     float* out_row = sOut + tid * kTcOutPitch;
+    const uint32_t sOut_s = tc::smem_u32(sOut);
     const uint32_t lane_base = static_cast<uint32_t>(warp * 32) << 16;
+    bool pending = false;  // C == 1: bulk stores may still be reading this warp's staged rows
+    bool issuer = false;   // this thread is the lane that issued them
     for (int tile = blockIdx.x; tile < tp.total_tiles; tile += gridDim.x) {
       const int b = tile / tp.tiles_per_utt, j = tile - b * tp.tiles_per_utt;
       const int32_t len = p.lengths[b];
       const int n_fr = frames_of(len, 320, 160);
       const int t_first = j * tp.tout;  // first OUTPUT frame of this tile; row i holds frame t_first - halo + i
       const bool active = t_first < n_fr;
-      if (tid == 0) {
-        if (j == 0 && p.n_frames) p.n_frames[b] = n_fr;
-        if (n_masks > 0) {
-          if (p.mask_table) {
-            for (int i = 0; i < 2 * n_masks; ++i) ctl->table[i] = p.mask_table[static_cast<size_t>(b) * 2 * n_masks + i];
-          } else {
-            int bad = specaug_draw_table(n_fr, 80, p.sa_F, p.n_masks_f, p.sa_T, p.sa_p, p.n_masks_t, p.seed,
-                                         p.first_utt + static_cast<uint64_t>(b), ctl->table);
-            if (bad && j == 0 && p.status) atomicOr(p.status, 1);
-          }
-        }
+      const int t_row = t_first - tp.halo + tid;
+      if (tid == 0 && j == 0 && p.n_frames) p.n_frames[b] = n_fr;
+      if (C == 1 && pending) {
+        if (issuer) tc::bulk_wait_read();  // async-groups belong to the thread that committed them
+        __syncwarp();
+        pending = false;
       }
       if (active) {
         if (!timed_out && !tc::mbar_wait(&ctl->acc_full, n & 1)) timed_out = true;
@@ -164,54 +215,47 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_frontend_kernel(const Kernel
         // 8 chunks of 8 accumulator columns (4 values of k1) per residue.  The butterfly code is one
         // rolled loop body; only the mel FFMAs (immediates, named accumulators) are per-chunk code,
         // selected by a warp-uniform switch - the whole epilogue stays inside the instruction cache.
-        float Q[6], P[20], d[5][8];
-#define TC_LOAD(COL)                                                                                     \
-  _Pragma("unroll") for (int r = 0; r < 5; ++r)                                                          \
-      tc::tmem_ld8(tmem_base + lane_base + (((5u * n + r) & 7u) << 6) + (COL), d[r]);
-        TC_LOAD(0)
-        tc::tmem_ld_wait();
-        {
-          float x[5];
-#pragma unroll
-          for (int r = 0; r < 5; ++r) x[r] = d[r][0];
-          tc_radix5_power_real(x, Q[0], Q[1], Q[2]);
-        }
-        {
-          // Y_r[32] = R_r * e^{-i pi r / 5}
-          const float cr[5] = {1.0f, 0.80901699437494742410f, 0.30901699437494742410f, -0.30901699437494742410f,
-                               -0.80901699437494742410f};
-          const float sr[5] = {0.0f, 0.58778525229247312917f, 0.95105651629515357212f, 0.95105651629515357212f,
-                               0.58778525229247312917f};
-          float xr[5], xi[5], p3, p4;
-#pragma unroll
-          for (int r = 0; r < 5; ++r) {
-            xr[r] = d[r][1] * cr[r];
-            xi[r] = -d[r][1] * sr[r];
-          }
-          tc_radix5_power(xr, xi, Q[3], Q[4], Q[5], p3, p4);
-        }
-#pragma unroll
-        for (int s = 1; s < 4; ++s) {
-          float xr[5], xi[5];
-#pragma unroll
-          for (int r = 0; r < 5; ++r) {
-            xr[r] = d[r][2 * s];
-            xi[r] = d[r][2 * s + 1];
-          }
-          tc_radix5_power(xr, xi, P[5 * s], P[5 * s + 1], P[5 * s + 2], P[5 * s + 3], P[5 * s + 4]);
-        }
-        TC_MEL_CHUNK_0(Q, P);
+        float P[20], d[5][8];
 #pragma unroll 1
-        for (int c = 1; c < 8; ++c) {
-          TC_LOAD(8 * c)
+        for (int c = 0; c < 8; ++c) {
+          float Q[6];
+#pragma unroll
+          for (int r = 0; r < 5; ++r)
+            tc::tmem_ld8(tmem_base + lane_base + (((5u * n + r) & 7u) << 6) + 8 * c, d[r]);
           tc::tmem_ld_wait();
           if (c == 7) {
             // all TMEM reads of this tile are done: hand the slots back before the remaining arithmetic
             tc::tc_fence_before();
             tc::mbar_arrive(&ctl->acc_empty);
           }
+          if (c == 0) {
+            // columns 0 / 1 hold the real k1 = 0 and k1 = 32 terms: Y_r[32] = R_r * e^{-i pi r / 5}
+            float x[5];
 #pragma unroll
-          for (int s = 0; s < 4; ++s) {
+            for (int r = 0; r < 5; ++r) x[r] = d[r][0];
+            tc_radix5_power_real(x, Q[0], Q[1], Q[2]);
+            const float cr[5] = {1.0f, 0.80901699437494742410f, 0.30901699437494742410f, -0.30901699437494742410f,
+                                 -0.80901699437494742410f};
+            const float sr[5] = {0.0f, 0.58778525229247312917f, 0.95105651629515357212f, 0.95105651629515357212f,
+                                 0.58778525229247312917f};
+            float xr[5], xi[5], p3, p4;
+#pragma unroll
+            for (int r = 0; r < 5; ++r) {
+              xr[r] = d[r][1] * cr[r];
+              xi[r] = -d[r][1] * sr[r];
+            }
+            tc_radix5_power(xr, xi, Q[3], Q[4], Q[5], p3, p4);
+          } else {
+            float xr[5], xi[5];
+#pragma unroll
+            for (int r = 0; r < 5; ++r) {
+              xr[r] = d[r][0];
+              xi[r] = d[r][1];
+            }
+            tc_radix5_power(xr, xi, P[0], P[1], P[2], P[3], P[4]);
+          }
+#pragma unroll
+          for (int s = 1; s < 4; ++s) {
             float xr[5], xi[5];
 #pragma unroll
             for (int r = 0; r < 5; ++r) {
@@ -221,6 +265,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_frontend_kernel(const Kernel
             tc_radix5_power(xr, xi, P[5 * s], P[5 * s + 1], P[5 * s + 2], P[5 * s + 3], P[5 * s + 4]);
           }
           switch (c) {
+            case 0: TC_MEL_CHUNK_0(Q, P); break;
             case 1: TC_MEL_CHUNK_1(Q, P); break;
             case 2: TC_MEL_CHUNK_2(Q, P); break;
             case 3: TC_MEL_CHUNK_3(Q, P); break;
@@ -230,60 +275,55 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_frontend_kernel(const Kernel
             default: TC_MEL_CHUNK_7(Q, P); break;
           }
         }
-#undef TC_LOAD
         TC_MEL_TAIL;
         ++n;
+        if (n_masks > 0 && t_row >= 0 && t_row < n_fr)
+          tc_mask_row(out_row, p.mask_table + static_cast<size_t>(b) * 2 * n_masks, p.n_masks_f, p.n_masks_t, t_row);
       }
-      tc::named_bar_sync(1, 128);  // staged rows + mask table visible to the 4 epilogue warps
 
-      // ---- copy-out: staged tile -> HBM with masks, delta, padding; 128-bit, fully coalesced ----
-      {
-        const int32_t* tbl = ctl->table;
-        float* out_b = p.out + static_cast<int64_t>(b) * p.t_max * 80 * C;
+      if (C == 1) {
+        // ---- each warp stores its own 32 staged rows: one 320-byte bulk copy per row, issued by
+        //      lane 0 (the rows are consecutive frames, so source and destination are affine in the
+        //      row index); there is no CTA-wide copy-out phase and no barrier between the warps ----
+        const int warp_u = __shfl_sync(0xffffffffu, warp, 0);  // provably warp-uniform: keeps the copies on the uniform datapath
+        const int t_warp = t_first + 32 * warp_u;
+        const int64_t rows_left = p.t_max - t_warp;
+        const int n_rows = rows_left >= 32 ? 32 : (rows_left > 0 ? static_cast<int>(rows_left) : 0);
+        if (n_rows > 0) {
+          if (t_row >= n_fr) tc_zero_row(out_row);  // padding is +0.0 (padded_batch, train.py:192-197)
+          tc::fence_async_smem();
+          __syncwarp();
+          if (tc::elect_one()) {
+            float* g = p.out + (static_cast<int64_t>(b) * p.t_max + t_warp) * 80;
+            const uint32_t s0 = sOut_s + 4 * kTcOutPitch * 32 * warp_u;
+#pragma unroll 4
+            for (int r = 0; r < n_rows; ++r) tc::bulk_copy_s2g(g + 80 * r, s0 + 4 * kTcOutPitch * r, 320);
+            tc::bulk_commit();
+            issuer = true;
+          }
+          pending = true;
+        }
+      } else {
+        tc::named_bar_sync(1, 128);  // staged (and masked) rows visible to the 4 epilogue warps
+        // ---- copy-out with delta / delta-delta: staged tile -> HBM, 128-bit, fully coalesced -----
+        float* out_b = p.out + static_cast<int64_t>(b) * p.t_max * 240;
         int i = tid / 20, quad = tid - 20 * i;
         for (int it = 0; it < 20; ++it) {
           const int t = t_first - tp.halo + i;
           if (i >= tp.halo && t < p.t_max) {
             float4 x0 = make_float4(0.f, 0.f, 0.f, 0.f), x1 = x0, x2 = x0;
-            const bool valid = t < n_fr;
-            if (valid) {
+            if (t < n_fr) {
               x0 = *reinterpret_cast<const float4*>(sOut + i * kTcOutPitch + 4 * quad);
-              if (n_masks) {
-                x0.x *= mask_value(tbl, p.n_masks_f, p.n_masks_t, t, 4 * quad + 0);
-                x0.y *= mask_value(tbl, p.n_masks_f, p.n_masks_t, t, 4 * quad + 1);
-                x0.z *= mask_value(tbl, p.n_masks_f, p.n_masks_t, t, 4 * quad + 2);
-                x0.w *= mask_value(tbl, p.n_masks_f, p.n_masks_t, t, 4 * quad + 3);
-              }
+              if (t >= 1) x1 = *reinterpret_cast<const float4*>(sOut + (i - 1) * kTcOutPitch + 4 * quad);
+              if (t >= 2) x2 = *reinterpret_cast<const float4*>(sOut + (i - 2) * kTcOutPitch + 4 * quad);
             }
-            if (C == 1) {
-              *reinterpret_cast<float4*>(out_b + static_cast<int64_t>(t) * 80 + 4 * quad) = x0;
-            } else {
-              if (valid && t >= 1) {
-                x1 = *reinterpret_cast<const float4*>(sOut + (i - 1) * kTcOutPitch + 4 * quad);
-                if (n_masks) {
-                  x1.x *= mask_value(tbl, p.n_masks_f, p.n_masks_t, t - 1, 4 * quad + 0);
-                  x1.y *= mask_value(tbl, p.n_masks_f, p.n_masks_t, t - 1, 4 * quad + 1);
-                  x1.z *= mask_value(tbl, p.n_masks_f, p.n_masks_t, t - 1, 4 * quad + 2);
-                  x1.w *= mask_value(tbl, p.n_masks_f, p.n_masks_t, t - 1, 4 * quad + 3);
-                }
-              }
-              if (valid && t >= 2) {
-                x2 = *reinterpret_cast<const float4*>(sOut + (i - 2) * kTcOutPitch + 4 * quad);
-                if (n_masks) {
-                  x2.x *= mask_value(tbl, p.n_masks_f, p.n_masks_t, t - 2, 4 * quad + 0);
-                  x2.y *= mask_value(tbl, p.n_masks_f, p.n_masks_t, t - 2, 4 * quad + 1);
-                  x2.z *= mask_value(tbl, p.n_masks_f, p.n_masks_t, t - 2, 4 * quad + 2);
-                  x2.w *= mask_value(tbl, p.n_masks_f, p.n_masks_t, t - 2, 4 * quad + 3);
-                }
-              }
-              // (x, x - x1, (x - x1) - (x1 - x2)) per channel, interleaved [.., m, 3]
-              const float dx = x0.x - x1.x, dy = x0.y - x1.y, dz = x0.z - x1.z, dw = x0.w - x1.w;
-              const float ex = x1.x - x2.x, ey = x1.y - x2.y, ez = x1.z - x2.z, ew = x1.w - x2.w;
-              float4* o = reinterpret_cast<float4*>(out_b + (static_cast<int64_t>(t) * 80 + 4 * quad) * 3);
-              o[0] = make_float4(x0.x, dx, dx - ex, x0.y);
-              o[1] = make_float4(dy, dy - ey, x0.z, dz);
-              o[2] = make_float4(dz - ez, x0.w, dw, dw - ew);
-            }
+            // (x, x - x1, (x - x1) - (x1 - x2)) per channel, interleaved [.., m, 3]
+            const float dx = x0.x - x1.x, dy = x0.y - x1.y, dz = x0.z - x1.z, dw = x0.w - x1.w;
+            const float ex = x1.x - x2.x, ey = x1.y - x2.y, ez = x1.z - x2.z, ew = x1.w - x2.w;
+            float4* o = reinterpret_cast<float4*>(out_b + (static_cast<int64_t>(t) * 80 + 4 * quad) * 3);
+            o[0] = make_float4(x0.x, dx, dx - ex, x0.y);
+            o[1] = make_float4(dy, dy - ey, x0.z, dz);
+            o[2] = make_float4(dz - ez, x0.w, dw, dw - ew);
           }
           quad += 8;
           i += 6;
@@ -292,9 +332,10 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_frontend_kernel(const Kernel
             i += 1;
           }
         }
+        tc::named_bar_sync(1, 128);  // the staging tile may be overwritten
       }
-      tc::named_bar_sync(1, 128);  // the staging tile and mask table may be overwritten
     }
+    if (C == 1 && issuer) tc::bulk_wait_all();
   }
 
   if (timed_out && p.status) atomicOr(p.status, 0x100);
@@ -303,7 +344,8 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_frontend_kernel(const Kernel
   if (warp == 8) tc::tmem_dealloc(tmem_base, 512);
 }
 
-// Host launcher.  Returns 0 on success.
+// Host launcher.  Returns 0 on success.  With SpecAugment enabled kp.mask_table must be set (the
+// API layer draws it with specaug_draw_kernel when the caller passes none).
 inline int tc_launch(const TcPlan& tc, const KernelParams& kp, int sm_count, cudaStream_t st) {
   TcParams tp;
   tp.b_image = tc.d_b;
