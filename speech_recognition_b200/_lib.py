@@ -9,7 +9,8 @@ import os
 import threading
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "lib", "libb200mel.so")
+# B200MEL_LIB: developer override used by experiments/run_variants.sh to A/B kernel variants
+LIB_PATH = os.environ.get("B200MEL_LIB") or os.path.join(HERE, "lib", "libb200mel.so")
 
 OK, ERR_INVALID_ARGUMENT, ERR_UNSUPPORTED, ERR_CUDA, ERR_NO_DEVICE = 0, 1, 2, 3, 4
 FEATURE_TYPES = {"spectrogram": 0, "log-mel-spectrogram": 1, "mfcc": 2}

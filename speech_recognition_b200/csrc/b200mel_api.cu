@@ -341,6 +341,7 @@ int b200mel_forward(b200mel_handle* h, const void* pcm, int32_t pcm_dtype, const
     }
     int rc = tc_launch(h->tc, kp, h->sm_count, st);
     if (tmp_table) cudaFreeAsync(tmp_table, st);
+    if (rc == 2) return fail(B200MEL_ERR_CUDA, "cuTensorMapEncodeTiled failed for the output tensor");
     if (rc != 0) return cuda_fail(cudaGetLastError(), "tc_frontend_kernel launch");
     h->launches.fetch_add(1);
     return B200MEL_OK;

@@ -26,6 +26,9 @@
 // (85 KB) and the output staging tile (42 KB).
 #pragma once
 
+#include <cuda.h>
+
+#include <cstring>
 #include <vector>
 
 #include "common.cuh"

@@ -63,8 +63,14 @@ __device__ __noinline__ void tc_produce_tile_slow(const short* __restrict__ pcm,
   }
 }
 
+#if defined(TC_ABLATE_PASSES)
+#define TC_FIRST_PS 2
+#else
+#define TC_FIRST_PS 0
+#endif
 template <int C>
-__global__ void __launch_bounds__(kTcThreads, 1) tc_frontend_kernel(const KernelParams p, const TcParams tp) {
+__global__ void __launch_bounds__(kTcThreads, 1)
+    tc_frontend_kernel(const KernelParams p, const TcParams tp, const __grid_constant__ CUtensorMap out_map) {
   extern __shared__ __align__(1024) uint8_t tc_smem_raw[];
   // 1024-byte alignment (swizzle atoms) without losing the shared address space of the pointer
   uint8_t* smem = tc_smem_raw + ((1024u - (tc::smem_u32(tc_smem_raw) & 1023u)) & 1023u);
@@ -109,7 +115,12 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_frontend_kernel(const Kernel
       const int64_t base = p.offsets ? p.offsets[b] : static_cast<int64_t>(b) * p.row_stride;
       const short* pcm = reinterpret_cast<const short*>(p.pcm) + base;
       const int32_t s_begin = 160 * (j * tp.tout - tp.halo);
+#if defined(TC_ABLATE_PROD)
+      if (n > 0 && !timed_out && !tc::mbar_wait(&ctl->a_empty, (n - 1) & 1)) timed_out = true;
+      if (false) {
+#else
       if ((reinterpret_cast<uintptr_t>(pcm) & 15) == 0) {
+#endif
         // 516 groups of 40 samples = 129 hops (128 frames + the half-row of overlap): four per thread,
         // the last four by threads 0..3.  All global loads are issued before the wait below, so the
         // DRAM latency overlaps the MMAs that are still reading the previous tile's streams.
@@ -139,8 +150,10 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_frontend_kernel(const Kernel
           tc_produce_group(raw[i][0], raw[i][1], raw[i][2], raw[i][3], raw[i][4], sA, ptid + 128 * i);
         if (ptid < 4) tc_produce_group(rawt[0], rawt[1], rawt[2], rawt[3], rawt[4], sA, ptid + 512);
       } else {
+#if !defined(TC_ABLATE_PROD)
         if (n > 0 && !timed_out && !tc::mbar_wait(&ctl->a_empty, (n - 1) & 1)) timed_out = true;
         tc_produce_tile_slow(pcm, s_begin, len, sA, ptid);
+#endif
       }
       tc::fence_async_smem();  // generic-proxy writes -> visible to the tensor core (async proxy)
       tc::mbar_arrive(&ctl->a_full);
@@ -168,14 +181,21 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_frontend_kernel(const Kernel
           }
           const uint32_t d_tmem = tmem_base + (((5u * n + r) & 7u) << 6);
           // passes, smallest magnitude first: lo x Bhi, hi x Blo, hi x Bhi
+#if defined(TC_ABLATE_MMA)
+          if (r >= 0) continue;
+#endif
 #pragma unroll
+#if defined(TC_ABLATE_PASSES)
+          for (int ps = 2; ps < 3; ++ps) {
+#else
           for (int ps = 0; ps < 3; ++ps) {
+#endif
             const int a_term = ps == 0 ? 1 : 0, b_term = ps == 1 ? 1 : 0;
 #pragma unroll
             for (int ks = 0; ks < 4; ++ks) {
               const uint32_t a_off = (a_term * 5 + r) * kTcStreamBytes + 32 * ks;
               const uint32_t b_off = (b_term * 5 + r) * kTcBBytes + 32 * ks;
-              tc::umma_f16(d_tmem, a_base + (a_off >> 4), b_base + (b_off >> 4), idesc, (ps | ks) ? 1u : 0u);
+              tc::umma_f16(d_tmem, a_base + (a_off >> 4), b_base + (b_off >> 4), idesc, (ps | ks) != (TC_FIRST_PS) ? 1u : 0u);
             }
           }
         }
@@ -216,8 +236,18 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_frontend_kernel(const Kernel
         // rolled loop body; only the mel FFMAs (immediates, named accumulators) are per-chunk code,
         // selected by a warp-uniform switch - the whole epilogue stays inside the instruction cache.
         float P[20], d[5][8];
+#if defined(TC_ABLATE_EPI)
+        // (experiment: epilogue arithmetic removed, pipeline floor of producers + MMA)
+        tc::tc_fence_before();
+        tc::mbar_arrive(&ctl->acc_empty);
+        for (int c = 8; c < 8; ++c) {
+#elif defined(TC_EPI_UNROLL)
+#pragma unroll
+        for (int c = 0; c < 8; ++c) {
+#else
 #pragma unroll 1
         for (int c = 0; c < 8; ++c) {
+#endif
           float Q[6];
 #pragma unroll
           for (int r = 0; r < 5; ++r)
@@ -282,22 +312,22 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_frontend_kernel(const Kernel
       }
 
       if (C == 1) {
-        // ---- each warp stores its own 32 staged rows: one 320-byte bulk copy per row, issued by
-        //      lane 0 (the rows are consecutive frames, so source and destination are affine in the
-        //      row index); there is no CTA-wide copy-out phase and no barrier between the warps ----
-        const int warp_u = __shfl_sync(0xffffffffu, warp, 0);  // provably warp-uniform: keeps the copies on the uniform datapath
+        // ---- each warp stores its own 32 staged rows with ONE TMA tensor store: the box is
+        //      [32 rows x 84 floats] (the padded staging pitch) over the [B, t_max, 80] output, so
+        //      the 4 pad floats of every row and the rows >= t_max fall outside the tensor and are
+        //      not written.  No CTA-wide copy-out phase, no barrier between the warps. ----
+        const int warp_u = __shfl_sync(0xffffffffu, warp, 0);  // provably warp-uniform
         const int t_warp = t_first + 32 * warp_u;
-        const int64_t rows_left = p.t_max - t_warp;
-        const int n_rows = rows_left >= 32 ? 32 : (rows_left > 0 ? static_cast<int>(rows_left) : 0);
-        if (n_rows > 0) {
+        if (t_warp < p.t_max) {
           if (t_row >= n_fr) tc_zero_row(out_row);  // padding is +0.0 (padded_batch, train.py:192-197)
           tc::fence_async_smem();
           __syncwarp();
+#if defined(TC_ABLATE_STORE)
+          if (false) {
+#else
           if (tc::elect_one()) {
-            float* g = p.out + (static_cast<int64_t>(b) * p.t_max + t_warp) * 80;
-            const uint32_t s0 = sOut_s + 4 * kTcOutPitch * 32 * warp_u;
-#pragma unroll 4
-            for (int r = 0; r < n_rows; ++r) tc::bulk_copy_s2g(g + 80 * r, s0 + 4 * kTcOutPitch * r, 320);
+#endif
+            tc::tma_store_3d(&out_map, sOut_s + 4 * kTcOutPitch * 32 * warp_u, 0, t_warp, b);
             tc::bulk_commit();
             issuer = true;
           }
@@ -344,6 +374,22 @@ __global__ void __launch_bounds__(kTcThreads, 1) tc_frontend_kernel(const Kernel
   if (warp == 8) tc::tmem_dealloc(tmem_base, 512);
 }
 
+// cuTensorMapEncodeTiled through the runtime's driver entry point (no link-time libcuda dependency).
+typedef CUresult (*TcEncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                    const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                    CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+inline TcEncodeTiledFn tc_encode_fn() {
+  static TcEncodeTiledFn fn = [] {
+    void* f = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &q) != cudaSuccess ||
+        q != cudaDriverEntryPointSuccess)
+      f = nullptr;
+    return reinterpret_cast<TcEncodeTiledFn>(f);
+  }();
+  return fn;
+}
+
 // Host launcher.  Returns 0 on success.  With SpecAugment enabled kp.mask_table must be set (the
 // API layer draws it with specaug_draw_kernel when the caller passes none).
 inline int tc_launch(const TcPlan& tc, const KernelParams& kp, int sm_count, cudaStream_t st) {
@@ -357,8 +403,23 @@ inline int tc_launch(const TcPlan& tc, const KernelParams& kp, int sm_count, cud
   if (total <= 0 || total > 0x7FFFFFFF) return total == 0 ? 0 : 1;
   tp.total_tiles = static_cast<int32_t>(total);
   const int grid = total < sm_count ? static_cast<int>(total) : sm_count;
-  if (kp.C == 3) tc_frontend_kernel<3><<<grid, kTcThreads, kTcSmemTotal, st>>>(kp, tp);
-  else tc_frontend_kernel<1><<<grid, kTcThreads, kTcSmemTotal, st>>>(kp, tp);
+  alignas(64) CUtensorMap map;
+  std::memset(&map, 0, sizeof(map));
+  if (kp.C == 3) {
+    tc_frontend_kernel<3><<<grid, kTcThreads, kTcSmemTotal, st>>>(kp, tp, map);
+  } else {
+    // output viewed as a 3-D tensor [B][t_max][80] f32; box = [1][32][84]
+    TcEncodeTiledFn enc = tc_encode_fn();
+    if (!enc) return 2;
+    const cuuint64_t dims[3] = {80, static_cast<cuuint64_t>(kp.t_max), static_cast<cuuint64_t>(kp.batch)};
+    const cuuint64_t strides[2] = {320, static_cast<cuuint64_t>(kp.t_max) * 320};
+    const cuuint32_t box[3] = {static_cast<cuuint32_t>(kTcOutPitch), 32, 1};
+    const cuuint32_t estr[3] = {1, 1, 1};
+    if (enc(&map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, kp.out, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+            CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+      return 2;
+    tc_frontend_kernel<1><<<grid, kTcThreads, kTcSmemTotal, st>>>(kp, tp, map);
+  }
   return cudaGetLastError() == cudaSuccess ? 0 : 1;
 }
 

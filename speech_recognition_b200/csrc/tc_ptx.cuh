@@ -105,6 +105,13 @@ __device__ __forceinline__ void named_bar_sync(uint32_t id, uint32_t nthreads) {
 __device__ __forceinline__ void bulk_copy_s2g(void* gdst, uint32_t ssrc, uint32_t bytes) {
   asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst), "r"(ssrc), "r"(bytes) : "memory");
 }
+// TMA tensor store shared -> global, 3-D tile mode: the box is dense in shared memory; box elements
+// outside the tensor's bounds are not written.
+__device__ __forceinline__ void tma_store_3d(const void* tmap, uint32_t ssrc, int c0, int c1, int c2) {
+  asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%1, %2, %3}], [%4];" ::"l"(tmap), "r"(c0),
+               "r"(c1), "r"(c2), "r"(ssrc)
+               : "memory");
+}
 // true in exactly one (elected) lane of a converged warp
 __device__ __forceinline__ bool elect_one() {
   uint32_t pred;
