@@ -47,11 +47,29 @@ __device__ __forceinline__ void tc_split_pair(uint32_t d, uint32_t& hi_out, uint
   lo_out = *reinterpret_cast<const uint32_t*>(&lo);
 }
 
-// One group: raw[5] = 40 samples -> 10 x 16-byte stores (stream (term, r), element block g).
-// Out of line on purpose: three call sites share one copy of the code (instruction-cache footprint).
-__device__ __noinline__ void tc_produce_group(uint4 r0, uint4 r1, uint4 r2, uint4 r3, uint4 r4, uint8_t* sA, int g) {
-  const uint4 raw[5] = {r0, r1, r2, r3, r4};
-  uint32_t w[20];
+// Swizzled byte offset of element block g (8 elements = 16 bytes) inside a stream: SWIZZLE_64B.
+__device__ __forceinline__ uint32_t tc_stream_offset(int g) {
+  const uint32_t o = 16u * static_cast<uint32_t>(g);
+  return o ^ (((o >> 7) & 3u) << 4);
+}
+
+// One (group, residue): w[20] = the group's 40 samples, already XOR-ed with 0x8000, two per word.
+// Stream R takes samples 5 e + R (e = 0..7): two 16-byte stores, (hi, lo) terms.
+template <int R>
+__device__ __forceinline__ void tc_produce_res(const uint32_t (&w)[20], uint8_t* sA, uint32_t ph) {
+  uint32_t hi[4], lo[4];
+#pragma unroll
+  for (int pi = 0; pi < 4; ++pi) {
+    const int a = 10 * pi + R, b = a + 5;  // sample indices of stream elements 2 pi, 2 pi + 1
+    const uint32_t sel = (2 * (a & 1)) | ((2 * (a & 1) + 1) << 4) | ((4 + 2 * (b & 1)) << 8) | ((5 + 2 * (b & 1)) << 12);
+    const uint32_t d = tc::prmt(w[a >> 1], w[b >> 1], sel);
+    tc_split_pair(d, hi[pi], lo[pi]);
+  }
+  *reinterpret_cast<uint4*>(sA + (0 * 5 + R) * kTcStreamBytes + ph) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+  *reinterpret_cast<uint4*>(sA + (1 * 5 + R) * kTcStreamBytes + ph) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+}
+
+__device__ __forceinline__ void tc_xor_words(const uint4 (&raw)[5], uint32_t (&w)[20]) {
 #pragma unroll
   for (int q = 0; q < 5; ++q) {
     w[4 * q + 0] = raw[q].x ^ 0x80008000u;
@@ -59,21 +77,19 @@ __device__ __noinline__ void tc_produce_group(uint4 r0, uint4 r1, uint4 r2, uint
     w[4 * q + 2] = raw[q].z ^ 0x80008000u;
     w[4 * q + 3] = raw[q].w ^ 0x80008000u;
   }
-  const uint32_t o = 16u * static_cast<uint32_t>(g);
-  const uint32_t ph = o ^ (((o >> 7) & 3u) << 4);  // SWIZZLE_64B on the stream's byte offset
-#pragma unroll
-  for (int r = 0; r < 5; ++r) {
-    uint32_t hi[4], lo[4];
-#pragma unroll
-    for (int pi = 0; pi < 4; ++pi) {
-      const int a = 10 * pi + r, b = a + 5;  // sample indices of stream elements 2 pi, 2 pi + 1
-      const uint32_t sel = (2 * (a & 1)) | ((2 * (a & 1) + 1) << 4) | ((4 + 2 * (b & 1)) << 8) | ((5 + 2 * (b & 1)) << 12);
-      const uint32_t d = tc::prmt(w[a >> 1], w[b >> 1], sel);
-      tc_split_pair(d, hi[pi], lo[pi]);
-    }
-    *reinterpret_cast<uint4*>(sA + (0 * 5 + r) * kTcStreamBytes + ph) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
-    *reinterpret_cast<uint4*>(sA + (1 * 5 + r) * kTcStreamBytes + ph) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
-  }
+}
+
+// One group, all residues (slow path only).  Out of line.
+__device__ __noinline__ void tc_produce_group(uint4 r0, uint4 r1, uint4 r2, uint4 r3, uint4 r4, uint8_t* sA, int g) {
+  const uint4 raw[5] = {r0, r1, r2, r3, r4};
+  uint32_t w[20];
+  tc_xor_words(raw, w);
+  const uint32_t ph = tc_stream_offset(g);
+  tc_produce_res<0>(w, sA, ph);
+  tc_produce_res<1>(w, sA, ph);
+  tc_produce_res<2>(w, sA, ph);
+  tc_produce_res<3>(w, sA, ph);
+  tc_produce_res<4>(w, sA, ph);
 }
 
 // ---------------------------------------------------------------------------------------------

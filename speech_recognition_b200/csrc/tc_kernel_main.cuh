@@ -4,10 +4,10 @@
 namespace b200mel {
 
 struct TcCtl {
-  uint64_t a_full;     // producers (128 arrivals) -> MMA: the A streams of this tile are in smem
-  uint64_t a_empty;    // tcgen05.commit -> producers: all MMAs that read the A streams are done
-  uint64_t acc_full;   // tcgen05.commit -> epilogue: the 5 accumulators of this tile are complete
-  uint64_t acc_empty;  // epilogue (128 arrivals) -> MMA: this tile's TMEM slots may be overwritten
+  uint64_t a_full[5];   // producers (128 arrivals) -> MMA: streams (hi, lo) of residue r are in smem
+  uint64_t a_empty[5];  // tcgen05.commit -> producers: the MMAs that read residue r's streams are done
+  uint64_t acc_full;    // tcgen05.commit -> epilogue: the 5 accumulators of this tile are complete
+  uint64_t acc_empty;   // epilogue (128 arrivals) -> MMA: this tile's TMEM slots may be overwritten
   uint32_t tmem_base;
 };
 
@@ -63,11 +63,6 @@ __device__ __noinline__ void tc_produce_tile_slow(const short* __restrict__ pcm,
   }
 }
 
-#if defined(TC_ABLATE_PASSES)
-#define TC_FIRST_PS 2
-#else
-#define TC_FIRST_PS 0
-#endif
 template <int C>
 __global__ void __launch_bounds__(kTcThreads, 1)
     tc_frontend_kernel(const KernelParams p, const TcParams tp, const __grid_constant__ CUtensorMap out_map) {
@@ -88,8 +83,10 @@ __global__ void __launch_bounds__(kTcThreads, 1)
     for (int i = tid; i < 10 * kTcBBytes / 16; i += kTcThreads) dst[i] = __ldg(src + i);
   }
   if (tid == 0) {
-    tc::mbar_init(&ctl->a_full, 128);
-    tc::mbar_init(&ctl->a_empty, 1);
+    for (int r = 0; r < 5; ++r) {
+      tc::mbar_init(&ctl->a_full[r], 128);
+      tc::mbar_init(&ctl->a_empty[r], 1);
+    }
     tc::mbar_init(&ctl->acc_full, 1);
     tc::mbar_init(&ctl->acc_empty, 128);
     tc::fence_mbar_init();
@@ -105,8 +102,16 @@ __global__ void __launch_bounds__(kTcThreads, 1)
 
   if (warp >= 4 && warp < 8) {
     // ======================= PRODUCERS (4 warps) ================================================
+    tc::setmaxnreg_dec<kTcRegsProducer>();
+    // The streams of residue r are refilled as soon as the MMAs of residue r of the previous tile
+    // have completed (a_empty[r]), while the tensor core is still busy with residues r+1..4: the
+    // conversion work of tile n+1 overlaps the MMAs of tile n although there is one A stage only.
     const int ptid = tid - 128;
     uint32_t n = 0;  // active tiles processed so far by this CTA
+    uint32_t ph[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) ph[i] = tc_stream_offset(ptid + 128 * i);
+    const uint32_t pht = tc_stream_offset(ptid + 512);
     for (int tile = blockIdx.x; tile < tp.total_tiles; tile += gridDim.x) {
       const int b = tile / tp.tiles_per_utt, j = tile - b * tp.tiles_per_utt;
       const int32_t len = p.lengths[b];
@@ -115,98 +120,97 @@ __global__ void __launch_bounds__(kTcThreads, 1)
       const int64_t base = p.offsets ? p.offsets[b] : static_cast<int64_t>(b) * p.row_stride;
       const short* pcm = reinterpret_cast<const short*>(p.pcm) + base;
       const int32_t s_begin = 160 * (j * tp.tout - tp.halo);
-#if defined(TC_ABLATE_PROD)
-      if (n > 0 && !timed_out && !tc::mbar_wait(&ctl->a_empty, (n - 1) & 1)) timed_out = true;
-      if (false) {
-#else
+      const uint32_t par = (n - 1) & 1;
       if ((reinterpret_cast<uintptr_t>(pcm) & 15) == 0) {
-#endif
         // 516 groups of 40 samples = 129 hops (128 frames + the half-row of overlap): four per thread,
-        // the last four by threads 0..3.  All global loads are issued before the wait below, so the
+        // the last four by threads 0..3.  All global loads are issued before the first wait, so the
         // DRAM latency overlaps the MMAs that are still reading the previous tile's streams.
         // Every frame t < n_fr ends at a multiple of 8 samples <= len, so clamping the 8-sample
         // block index into [0, len/8 - 1] never changes a sample a valid frame uses; blocks outside
         // only feed rows that the epilogue zero-fills (t >= n_fr) or drops (t < 0).
         const uint4* src = reinterpret_cast<const uint4*>(pcm);
         const int32_t blk_max = (len >> 3) - 1;  // n_fr >= 1 here, so len >= 320
-        uint4 raw[4][5], rawt[5];
+        uint32_t w[4][20], wt[20];
 #pragma unroll
-        for (int i = 0; i < 4; ++i)
+        for (int i = 0; i < 4; ++i) {
+          uint4 raw[5];
 #pragma unroll
           for (int q = 0; q < 5; ++q) {
             const int32_t blk = (s_begin >> 3) + 5 * (ptid + 128 * i) + q;
-            raw[i][q] = __ldg(src + min(max(blk, 0), blk_max));
+            raw[q] = __ldg(src + min(max(blk, 0), blk_max));
           }
+          tc_xor_words(raw, w[i]);
+        }
         if (ptid < 4) {
+          uint4 raw[5];
 #pragma unroll
           for (int q = 0; q < 5; ++q) {
             const int32_t blk = (s_begin >> 3) + 5 * (ptid + 512) + q;
-            rawt[q] = __ldg(src + min(max(blk, 0), blk_max));
+            raw[q] = __ldg(src + min(max(blk, 0), blk_max));
           }
+          tc_xor_words(raw, wt);
         }
-        if (n > 0 && !timed_out && !tc::mbar_wait(&ctl->a_empty, (n - 1) & 1)) timed_out = true;
-#pragma unroll
-        for (int i = 0; i < 4; ++i)
-          tc_produce_group(raw[i][0], raw[i][1], raw[i][2], raw[i][3], raw[i][4], sA, ptid + 128 * i);
-        if (ptid < 4) tc_produce_group(rawt[0], rawt[1], rawt[2], rawt[3], rawt[4], sA, ptid + 512);
+#define TC_PRODUCE_RES(R)                                                                              \
+  if (n > 0 && !timed_out && !tc::mbar_wait(&ctl->a_empty[R], par)) timed_out = true;                  \
+  _Pragma("unroll") for (int i = 0; i < 4; ++i) tc_produce_res<R>(w[i], sA, ph[i]);                    \
+  if (ptid < 4) tc_produce_res<R>(wt, sA, pht);                                                        \
+  tc::fence_async_smem(); /* generic-proxy writes -> visible to the tensor core (async proxy) */       \
+  tc::mbar_arrive(&ctl->a_full[R]);
+        TC_PRODUCE_RES(0)
+        TC_PRODUCE_RES(1)
+        TC_PRODUCE_RES(2)
+        TC_PRODUCE_RES(3)
+        TC_PRODUCE_RES(4)
+#undef TC_PRODUCE_RES
       } else {
-#if !defined(TC_ABLATE_PROD)
-        if (n > 0 && !timed_out && !tc::mbar_wait(&ctl->a_empty, (n - 1) & 1)) timed_out = true;
+        for (int r = 0; r < 5; ++r)
+          if (n > 0 && !timed_out && !tc::mbar_wait(&ctl->a_empty[r], par)) timed_out = true;
         tc_produce_tile_slow(pcm, s_begin, len, sA, ptid);
-#endif
+        tc::fence_async_smem();
+        for (int r = 0; r < 5; ++r) tc::mbar_arrive(&ctl->a_full[r]);
       }
-      tc::fence_async_smem();  // generic-proxy writes -> visible to the tensor core (async proxy)
-      tc::mbar_arrive(&ctl->a_full);
       ++n;
     }
-  } else if (warp == 8) {
-    // ======================= MMA ISSUER =========================================================
-    uint32_t n = 0;
-    const uint32_t idesc = tc::make_idesc_f16(128, 64);
-    const uint64_t a_base = tc::make_smem_desc(tc::smem_u32(sA), 16, 512, tc::kLayoutSw64);
-    const uint64_t b_base = tc::make_smem_desc(tc::smem_u32(sB), 16, 1024, tc::kLayoutSw128);
-    for (int tile = blockIdx.x; tile < tp.total_tiles; tile += gridDim.x) {
-      const int b = tile / tp.tiles_per_utt, j = tile - b * tp.tiles_per_utt;
-      const int n_fr = frames_of(p.lengths[b], 320, 160);
-      if (j * tp.tout >= n_fr) continue;
-      if (!timed_out && !tc::mbar_wait(&ctl->a_full, n & 1)) timed_out = true;
-      tc::tc_fence_after();
-      if (lane == 0) {
+  } else if (warp >= 8) {
+    // ======================= MMA ISSUER (one thread of warp 8) ==================================
+    tc::setmaxnreg_dec<kTcRegsMma>();
+    if (warp == 8 && lane == 0) {
+      uint32_t n = 0;
+      const uint32_t idesc = tc::make_idesc_f16(128, 64);
+      const uint64_t a_base = tc::make_smem_desc(tc::smem_u32(sA), 16, 512, tc::kLayoutSw64);
+      const uint64_t b_base = tc::make_smem_desc(tc::smem_u32(sB), 16, 1024, tc::kLayoutSw128);
+      for (int tile = blockIdx.x; tile < tp.total_tiles; tile += gridDim.x) {
+        const int b = tile / tp.tiles_per_utt, j = tile - b * tp.tiles_per_utt;
+        const int n_fr = frames_of(p.lengths[b], 320, 160);
+        if (j * tp.tout >= n_fr) continue;
 #pragma unroll 1
         for (int r = 0; r < 5; ++r) {
+          if (!timed_out && !tc::mbar_wait(&ctl->a_full[r], n & 1)) timed_out = true;
           // slots of residues 3, 4 were residues 0, 1 of the previous tile: wait for its epilogue
-          if (r == 3 && n > 0) {
-            if (!timed_out && !tc::mbar_wait(&ctl->acc_empty, (n - 1) & 1)) timed_out = true;
-            tc::tc_fence_after();
-          }
+          if (r == 3 && n > 0 && !timed_out && !tc::mbar_wait(&ctl->acc_empty, (n - 1) & 1)) timed_out = true;
+          tc::tc_fence_after();
           const uint32_t d_tmem = tmem_base + (((5u * n + r) & 7u) << 6);
           // passes, smallest magnitude first: lo x Bhi, hi x Blo, hi x Bhi
-#if defined(TC_ABLATE_MMA)
-          if (r >= 0) continue;
-#endif
 #pragma unroll
-#if defined(TC_ABLATE_PASSES)
-          for (int ps = 2; ps < 3; ++ps) {
-#else
           for (int ps = 0; ps < 3; ++ps) {
-#endif
             const int a_term = ps == 0 ? 1 : 0, b_term = ps == 1 ? 1 : 0;
 #pragma unroll
             for (int ks = 0; ks < 4; ++ks) {
               const uint32_t a_off = (a_term * 5 + r) * kTcStreamBytes + 32 * ks;
               const uint32_t b_off = (b_term * 5 + r) * kTcBBytes + 32 * ks;
-              tc::umma_f16(d_tmem, a_base + (a_off >> 4), b_base + (b_off >> 4), idesc, (ps | ks) != (TC_FIRST_PS) ? 1u : 0u);
+              tc::umma_f16(d_tmem, a_base + (a_off >> 4), b_base + (b_off >> 4), idesc, (ps | ks) ? 1u : 0u);
             }
           }
+          tc::umma_commit(&ctl->a_empty[r]);  // residue r's streams may be refilled
         }
         tc::umma_commit(&ctl->acc_full);
-        tc::umma_commit(&ctl->a_empty);
+        ++n;
       }
-      __syncwarp();
-      ++n;
     }
+    __syncwarp();
   } else {
     // ======================= EPILOGUE (warps 0-3: thread = frame row = TMEM lane) ===============
+    tc::setmaxnreg_inc<kTcRegsEpilogue>();
     uint32_t n = 0;
     const float eps = p.epsilon, log_eps = tp.log_eps;
     const int n_masks = p.n_masks_f + p.n_masks_t;
@@ -232,37 +236,42 @@ __global__ void __launch_bounds__(kTcThreads, 1)
         if (!timed_out && !tc::mbar_wait(&ctl->acc_full, n & 1)) timed_out = true;
         tc::tc_fence_after();
         TC_DECL_ACC
-        // 8 chunks of 8 accumulator columns (4 values of k1) per residue.  The butterfly code is one
-        // rolled loop body; only the mel FFMAs (immediates, named accumulators) are per-chunk code,
-        // selected by a warp-uniform switch - the whole epilogue stays inside the instruction cache.
-        float P[20], d[5][8];
+        // 8 chunks of 8 accumulator columns (4 values of k1) per residue, two TMEM register buffers:
+        // the loads of chunk c+1 are in flight while chunk c is computed.  The butterfly code is a
+        // rolled loop over chunk pairs; only the mel FFMAs (immediates, named accumulators) are
+        // per-chunk code, selected by a warp-uniform switch.
+        float P[20], dA[5][8], dB[5][8];
+        const uint32_t t_tile = tmem_base + lane_base;
+#define TC_LOAD(D, CH)                                                                            \
+  _Pragma("unroll") for (int r = 0; r < 5; ++r) tc::tmem_ld8(t_tile + (((5u * n + r) & 7u) << 6) + 8 * (CH), D[r]);
+#define TC_RADIX_STEP(D, S)                                                                       \
+  {                                                                                               \
+    float xr[5], xi[5];                                                                           \
+    _Pragma("unroll") for (int r = 0; r < 5; ++r) {                                               \
+      xr[r] = D[r][2 * (S)];                                                                      \
+      xi[r] = D[r][2 * (S) + 1];                                                                  \
+    }                                                                                             \
+    tc_radix5_power(xr, xi, P[5 * (S)], P[5 * (S) + 1], P[5 * (S) + 2], P[5 * (S) + 3], P[5 * (S) + 4]); \
+  }
 #if defined(TC_ABLATE_EPI)
         // (experiment: epilogue arithmetic removed, pipeline floor of producers + MMA)
         tc::tc_fence_before();
         tc::mbar_arrive(&ctl->acc_empty);
-        for (int c = 8; c < 8; ++c) {
-#elif defined(TC_EPI_UNROLL)
-#pragma unroll
-        for (int c = 0; c < 8; ++c) {
+        for (int c = 8; c < 8; c += 2) {
 #else
+        TC_LOAD(dA, 0)
 #pragma unroll 1
-        for (int c = 0; c < 8; ++c) {
+        for (int c = 0; c < 8; c += 2) {
 #endif
+          // ---- even chunk c from dA; prefetch chunk c + 1 into dB
           float Q[6];
-#pragma unroll
-          for (int r = 0; r < 5; ++r)
-            tc::tmem_ld8(tmem_base + lane_base + (((5u * n + r) & 7u) << 6) + 8 * c, d[r]);
           tc::tmem_ld_wait();
-          if (c == 7) {
-            // all TMEM reads of this tile are done: hand the slots back before the remaining arithmetic
-            tc::tc_fence_before();
-            tc::mbar_arrive(&ctl->acc_empty);
-          }
+          TC_LOAD(dB, c + 1)
           if (c == 0) {
             // columns 0 / 1 hold the real k1 = 0 and k1 = 32 terms: Y_r[32] = R_r * e^{-i pi r / 5}
             float x[5];
 #pragma unroll
-            for (int r = 0; r < 5; ++r) x[r] = d[r][0];
+            for (int r = 0; r < 5; ++r) x[r] = dA[r][0];
             tc_radix5_power_real(x, Q[0], Q[1], Q[2]);
             const float cr[5] = {1.0f, 0.80901699437494742410f, 0.30901699437494742410f, -0.30901699437494742410f,
                                  -0.80901699437494742410f};
@@ -271,40 +280,44 @@ __global__ void __launch_bounds__(kTcThreads, 1)
             float xr[5], xi[5], p3, p4;
 #pragma unroll
             for (int r = 0; r < 5; ++r) {
-              xr[r] = d[r][1] * cr[r];
-              xi[r] = -d[r][1] * sr[r];
+              xr[r] = dA[r][1] * cr[r];
+              xi[r] = -dA[r][1] * sr[r];
             }
             tc_radix5_power(xr, xi, Q[3], Q[4], Q[5], p3, p4);
           } else {
-            float xr[5], xi[5];
-#pragma unroll
-            for (int r = 0; r < 5; ++r) {
-              xr[r] = d[r][0];
-              xi[r] = d[r][1];
-            }
-            tc_radix5_power(xr, xi, P[0], P[1], P[2], P[3], P[4]);
+            TC_RADIX_STEP(dA, 0)
           }
-#pragma unroll
-          for (int s = 1; s < 4; ++s) {
-            float xr[5], xi[5];
-#pragma unroll
-            for (int r = 0; r < 5; ++r) {
-              xr[r] = d[r][2 * s];
-              xi[r] = d[r][2 * s + 1];
-            }
-            tc_radix5_power(xr, xi, P[5 * s], P[5 * s + 1], P[5 * s + 2], P[5 * s + 3], P[5 * s + 4]);
-          }
+          TC_RADIX_STEP(dA, 1)
+          TC_RADIX_STEP(dA, 2)
+          TC_RADIX_STEP(dA, 3)
           switch (c) {
             case 0: TC_MEL_CHUNK_0(Q, P); break;
-            case 1: TC_MEL_CHUNK_1(Q, P); break;
             case 2: TC_MEL_CHUNK_2(Q, P); break;
-            case 3: TC_MEL_CHUNK_3(Q, P); break;
             case 4: TC_MEL_CHUNK_4(Q, P); break;
-            case 5: TC_MEL_CHUNK_5(Q, P); break;
-            case 6: TC_MEL_CHUNK_6(Q, P); break;
+            default: TC_MEL_CHUNK_6(Q, P); break;
+          }
+          // ---- odd chunk c + 1 from dB; prefetch chunk c + 2 into dA
+          tc::tmem_ld_wait();
+          if (c < 6) {
+            TC_LOAD(dA, c + 2)
+          } else {
+            // all TMEM reads of this tile are done: hand the slots back before the remaining arithmetic
+            tc::tc_fence_before();
+            tc::mbar_arrive(&ctl->acc_empty);
+          }
+          TC_RADIX_STEP(dB, 0)
+          TC_RADIX_STEP(dB, 1)
+          TC_RADIX_STEP(dB, 2)
+          TC_RADIX_STEP(dB, 3)
+          switch (c) {
+            case 0: TC_MEL_CHUNK_1(Q, P); break;
+            case 2: TC_MEL_CHUNK_3(Q, P); break;
+            case 4: TC_MEL_CHUNK_5(Q, P); break;
             default: TC_MEL_CHUNK_7(Q, P); break;
           }
         }
+#undef TC_LOAD
+#undef TC_RADIX_STEP
         TC_MEL_TAIL;
         ++n;
         if (n_masks > 0 && t_row >= 0 && t_row < n_fr)
