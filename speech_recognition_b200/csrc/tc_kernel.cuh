@@ -47,10 +47,12 @@ constexpr int kTcSmemOut = kTcSmemA + 10 * kTcStreamBytes;     // 168960
 constexpr int kTcOutPitch = 84;                                // floats per staged row (16-B aligned, conflict-free)
 constexpr int kTcSmemCtl = kTcSmemOut + kTcTileM * kTcOutPitch * 4;  // 211968
 constexpr int kTcSmemTotal = kTcSmemCtl + 256 + 1024;          // + control block + alignment slack
-// Three warpgroups: epilogue (warps 0-3), producers (4-7), MMA issuer (warp 8; 9-11 idle).  Registers
-// are re-balanced between them with setmaxnreg: a 9-warp CTA would cap every thread at 168.
-constexpr int kTcThreads = 384;
-constexpr int kTcRegsEpilogue = 232, kTcRegsProducer = 136, kTcRegsMma = 40;
+// Four warpgroups: epilogue groups A and B (warps 0-3, 4-7), producers (8-11), MMA issuer (warp 12;
+// 13-15 idle).  The launch allocates 128 registers per thread; setmaxnreg moves the idle warpgroup's
+// share to the others (per SM sub-partition: 2 x 168 + 136 + 40 = 512).
+constexpr int kTcThreads = 512;
+constexpr int kTcMmaWarp = 12;
+constexpr int kTcRegsEpilogue = 168, kTcRegsProducer = 136, kTcRegsMma = 40;
 constexpr int kTcBScaleLog2 = 10;          // B is stored as 2^10 * w * twiddle
 // power = |Y|^2 * 2^(-2*10) (B scale) * 2^(-30) (int16 -> [-1, 1) twice)
 #define TC_PSCALE 0x1p-50f

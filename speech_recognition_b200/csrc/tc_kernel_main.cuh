@@ -19,6 +19,10 @@ __device__ __forceinline__ float tc_finish(float acc, float eps, float log_eps) 
   return acc == 0.0f ? log_eps : l2 * 0.69314718055994530942f;
 }
 
+#define TC_FINISH1(M_, A) out_row[M_] = tc_finish(A, eps, log_eps)
+// shared bins: group A parks its partial sum in the staged row, group B adds its own and finishes
+#define TC_PART1(M_, A) out_row[M_] = (A)
+#define TC_SHARED1(M_, A) out_row[M_] = tc_finish((A) + out_row[M_], eps, log_eps)
 #define TC_FINISH4(G, A, B, C, D)                                                              \
   *reinterpret_cast<float4*>(out_row + 4 * (G)) =                                              \
       make_float4(tc_finish(A, eps, log_eps), tc_finish(B, eps, log_eps), tc_finish(C, eps, log_eps), \
@@ -88,25 +92,25 @@ __global__ void __launch_bounds__(kTcThreads, 1)
       tc::mbar_init(&ctl->a_empty[r], 1);
     }
     tc::mbar_init(&ctl->acc_full, 1);
-    tc::mbar_init(&ctl->acc_empty, 128);
+    tc::mbar_init(&ctl->acc_empty, 256);
     tc::fence_mbar_init();
   }
   tc::fence_async_smem();
   __syncthreads();
-  if (warp == 8) tc::tmem_alloc(&ctl->tmem_base, 512);
+  if (warp == kTcMmaWarp) tc::tmem_alloc(&ctl->tmem_base, 512);
   tc::tc_fence_before();
   __syncthreads();
   tc::tc_fence_after();
   const uint32_t tmem_base = ctl->tmem_base;
   bool timed_out = false;
 
-  if (warp >= 4 && warp < 8) {
-    // ======================= PRODUCERS (4 warps) ================================================
-    tc::setmaxnreg_dec<kTcRegsProducer>();
+  if (warp >= 8 && warp < 12) {
+    // ======================= PRODUCERS (warps 8-11) =============================================
+    tc::setmaxnreg_inc<kTcRegsProducer>();
+    const int ptid = tid - 256;
     // The streams of residue r are refilled as soon as the MMAs of residue r of the previous tile
     // have completed (a_empty[r]), while the tensor core is still busy with residues r+1..4: the
     // conversion work of tile n+1 overlaps the MMAs of tile n although there is one A stage only.
-    const int ptid = tid - 128;
     uint32_t n = 0;  // active tiles processed so far by this CTA
     uint32_t ph[4];
 #pragma unroll
@@ -171,10 +175,10 @@ __global__ void __launch_bounds__(kTcThreads, 1)
       }
       ++n;
     }
-  } else if (warp >= 8) {
-    // ======================= MMA ISSUER (one thread of warp 8) ==================================
+  } else if (warp >= 12) {
+    // ======================= MMA ISSUER (one thread of warp 12; warps 13-15 idle) ===============
     tc::setmaxnreg_dec<kTcRegsMma>();
-    if (warp == 8 && lane == 0) {
+    if (warp == kTcMmaWarp && lane == 0) {
       uint32_t n = 0;
       const uint32_t idesc = tc::make_idesc_f16(128, 64);
       const uint64_t a_base = tc::make_smem_desc(tc::smem_u32(sA), 16, 512, tc::kLayoutSw64);
@@ -209,69 +213,78 @@ __global__ void __launch_bounds__(kTcThreads, 1)
     }
     __syncwarp();
   } else {
-    // ======================= EPILOGUE (warps 0-3: thread = frame row = TMEM lane) ===============
+    // ======================= EPILOGUE (warps 0-7) ===============================================
+    // thread = frame row = TMEM lane.  Two groups share every tile: group A (warps 0-3) reduces
+    // accumulator columns 0-31 of each residue (k1 = 0, 32, 1..15), group B (warps 4-7) columns
+    // 32-63 (k1 = 16..31); warps w and w + 4 work on the same 32 rows.  Each mel bin is finished by
+    // the group that feeds it; the 13 bins fed by both are parked by A in the staged row and
+    // finished by B after the pair barrier.  B then stores the 32 rows with one TMA tensor store.
     tc::setmaxnreg_inc<kTcRegsEpilogue>();
+    const int group = warp >> 2, wq = warp & 3;
+    const int row = wq * 32 + lane;
     uint32_t n = 0;
     const float eps = p.epsilon, log_eps = tp.log_eps;
     const int n_masks = p.n_masks_f + p.n_masks_t;
-    float* out_row = sOut + tid * kTcOutPitch;
+    float* out_row = sOut + row * kTcOutPitch;
     const uint32_t sOut_s = tc::smem_u32(sOut);
-    const uint32_t lane_base = static_cast<uint32_t>(warp * 32) << 16;
-    bool pending = false;  // C == 1: bulk stores may still be reading this warp's staged rows
-    bool issuer = false;   // this thread is the lane that issued them
+    const uint32_t lane_base = static_cast<uint32_t>(wq * 32) << 16;
+    const uint32_t bar_ready = 1 + wq, bar_free = 5 + wq;  // pair barriers (64 threads)
+    bool pending = false;  // C == 1: the pair's previous TMA store may still be reading the staged rows
+    bool issuer = false;   // this thread issued it (bulk async-groups are per thread)
     for (int tile = blockIdx.x; tile < tp.total_tiles; tile += gridDim.x) {
       const int b = tile / tp.tiles_per_utt, j = tile - b * tp.tiles_per_utt;
       const int32_t len = p.lengths[b];
       const int n_fr = frames_of(len, 320, 160);
       const int t_first = j * tp.tout;  // first OUTPUT frame of this tile; row i holds frame t_first - halo + i
       const bool active = t_first < n_fr;
-      const int t_row = t_first - tp.halo + tid;
+      const int t_row = t_first - tp.halo + row;
       if (tid == 0 && j == 0 && p.n_frames) p.n_frames[b] = n_fr;
       if (C == 1 && pending) {
-        if (issuer) tc::bulk_wait_read();  // async-groups belong to the thread that committed them
-        __syncwarp();
+        // B: the staged rows are free once the previous store has read them; A waits for that
+        if (group == 1) {
+          if (issuer) tc::bulk_wait_read();
+          __syncwarp();
+          tc::named_bar_arrive(bar_free, 64);
+        } else {
+          tc::named_bar_sync(bar_free, 64);
+        }
         pending = false;
       }
       if (active) {
         if (!timed_out && !tc::mbar_wait(&ctl->acc_full, n & 1)) timed_out = true;
         tc::tc_fence_after();
         TC_DECL_ACC
-        // 8 chunks of 8 accumulator columns (4 values of k1) per residue, two TMEM register buffers:
-        // the loads of chunk c+1 are in flight while chunk c is computed.  The butterfly code is a
-        // rolled loop over chunk pairs; only the mel FFMAs (immediates, named accumulators) are
-        // per-chunk code, selected by a warp-uniform switch.
-        float P[20], dA[5][8], dB[5][8];
+        float P[20], Q[6], d[5][8];
         const uint32_t t_tile = tmem_base + lane_base;
-#define TC_LOAD(D, CH)                                                                            \
-  _Pragma("unroll") for (int r = 0; r < 5; ++r) tc::tmem_ld8(t_tile + (((5u * n + r) & 7u) << 6) + 8 * (CH), D[r]);
-#define TC_RADIX_STEP(D, S)                                                                       \
+        // one rolled loop per group over its 4 chunks of 8 accumulator columns (4 values of k1) per
+        // residue; only the mel FFMAs (immediates, named accumulators) are per-chunk code
+#define TC_RADIX_STEP(S)                                                                          \
   {                                                                                               \
     float xr[5], xi[5];                                                                           \
     _Pragma("unroll") for (int r = 0; r < 5; ++r) {                                               \
-      xr[r] = D[r][2 * (S)];                                                                      \
-      xi[r] = D[r][2 * (S) + 1];                                                                  \
+      xr[r] = d[r][2 * (S)];                                                                      \
+      xi[r] = d[r][2 * (S) + 1];                                                                  \
     }                                                                                             \
     tc_radix5_power(xr, xi, P[5 * (S)], P[5 * (S) + 1], P[5 * (S) + 2], P[5 * (S) + 3], P[5 * (S) + 4]); \
   }
-#if defined(TC_ABLATE_EPI)
-        // (experiment: epilogue arithmetic removed, pipeline floor of producers + MMA)
-        tc::tc_fence_before();
-        tc::mbar_arrive(&ctl->acc_empty);
-        for (int c = 8; c < 8; c += 2) {
-#else
-        TC_LOAD(dA, 0)
+#define TC_LOAD_CHUNK(CH)                                                                         \
+  _Pragma("unroll") for (int r = 0; r < 5; ++r) tc::tmem_ld8(t_tile + (((5u * n + r) & 7u) << 6) + 8 * (CH), d[r]); \
+  tc::tmem_ld_wait();                                                                             \
+  if (((CH) & 3) == 3) {                                                                          \
+    /* this thread's TMEM reads of the tile are done: hand the slots back before the arithmetic */ \
+    tc::tc_fence_before();                                                                        \
+    tc::mbar_arrive(&ctl->acc_empty);                                                             \
+  }
+        // both groups run the SAME loop code (instruction-cache footprint): group A chunks 0-3, B 4-7
+        const int c0 = 4 * group;
 #pragma unroll 1
-        for (int c = 0; c < 8; c += 2) {
-#endif
-          // ---- even chunk c from dA; prefetch chunk c + 1 into dB
-          float Q[6];
-          tc::tmem_ld_wait();
-          TC_LOAD(dB, c + 1)
+        for (int c = c0; c < c0 + 4; ++c) {
+          TC_LOAD_CHUNK(c)
           if (c == 0) {
             // columns 0 / 1 hold the real k1 = 0 and k1 = 32 terms: Y_r[32] = R_r * e^{-i pi r / 5}
             float x[5];
 #pragma unroll
-            for (int r = 0; r < 5; ++r) x[r] = dA[r][0];
+            for (int r = 0; r < 5; ++r) x[r] = d[r][0];
             tc_radix5_power_real(x, Q[0], Q[1], Q[2]);
             const float cr[5] = {1.0f, 0.80901699437494742410f, 0.30901699437494742410f, -0.30901699437494742410f,
                                  -0.80901699437494742410f};
@@ -280,78 +293,66 @@ __global__ void __launch_bounds__(kTcThreads, 1)
             float xr[5], xi[5], p3, p4;
 #pragma unroll
             for (int r = 0; r < 5; ++r) {
-              xr[r] = dA[r][1] * cr[r];
-              xi[r] = -dA[r][1] * sr[r];
+              xr[r] = d[r][1] * cr[r];
+              xi[r] = -d[r][1] * sr[r];
             }
             tc_radix5_power(xr, xi, Q[3], Q[4], Q[5], p3, p4);
           } else {
-            TC_RADIX_STEP(dA, 0)
+            TC_RADIX_STEP(0)
           }
-          TC_RADIX_STEP(dA, 1)
-          TC_RADIX_STEP(dA, 2)
-          TC_RADIX_STEP(dA, 3)
+          TC_RADIX_STEP(1)
+          TC_RADIX_STEP(2)
+          TC_RADIX_STEP(3)
           switch (c) {
             case 0: TC_MEL_CHUNK_0(Q, P); break;
+            case 1: TC_MEL_CHUNK_1(Q, P); break;
             case 2: TC_MEL_CHUNK_2(Q, P); break;
+            case 3: TC_MEL_CHUNK_3(Q, P); break;
             case 4: TC_MEL_CHUNK_4(Q, P); break;
-            default: TC_MEL_CHUNK_6(Q, P); break;
-          }
-          // ---- odd chunk c + 1 from dB; prefetch chunk c + 2 into dA
-          tc::tmem_ld_wait();
-          if (c < 6) {
-            TC_LOAD(dA, c + 2)
-          } else {
-            // all TMEM reads of this tile are done: hand the slots back before the remaining arithmetic
-            tc::tc_fence_before();
-            tc::mbar_arrive(&ctl->acc_empty);
-          }
-          TC_RADIX_STEP(dB, 0)
-          TC_RADIX_STEP(dB, 1)
-          TC_RADIX_STEP(dB, 2)
-          TC_RADIX_STEP(dB, 3)
-          switch (c) {
-            case 0: TC_MEL_CHUNK_1(Q, P); break;
-            case 2: TC_MEL_CHUNK_3(Q, P); break;
-            case 4: TC_MEL_CHUNK_5(Q, P); break;
+            case 5: TC_MEL_CHUNK_5(Q, P); break;
+            case 6: TC_MEL_CHUNK_6(Q, P); break;
             default: TC_MEL_CHUNK_7(Q, P); break;
           }
         }
-#undef TC_LOAD
+        if (group == 1) {
+          // A's finished bins and parked partial sums of this row are in shared memory
+          tc::named_bar_sync(bar_ready, 64);
+          TC_MEL_SHARED_B;
+          if (n_masks > 0 && t_row >= 0 && t_row < n_fr)
+            tc_mask_row(out_row, p.mask_table + static_cast<size_t>(b) * 2 * n_masks, p.n_masks_f, p.n_masks_t, t_row);
+        }
+#undef TC_LOAD_CHUNK
 #undef TC_RADIX_STEP
-        TC_MEL_TAIL;
+        if (group == 0) tc::named_bar_arrive(bar_ready, 64);
         ++n;
-        if (n_masks > 0 && t_row >= 0 && t_row < n_fr)
-          tc_mask_row(out_row, p.mask_table + static_cast<size_t>(b) * 2 * n_masks, p.n_masks_f, p.n_masks_t, t_row);
       }
 
       if (C == 1) {
-        // ---- each warp stores its own 32 staged rows with ONE TMA tensor store: the box is
+        // ---- group B stores the pair's 32 staged rows with ONE TMA tensor store: the box is
         //      [32 rows x 84 floats] (the padded staging pitch) over the [B, t_max, 80] output, so
         //      the 4 pad floats of every row and the rows >= t_max fall outside the tensor and are
-        //      not written.  No CTA-wide copy-out phase, no barrier between the warps. ----
-        const int warp_u = __shfl_sync(0xffffffffu, warp, 0);  // provably warp-uniform
-        const int t_warp = t_first + 32 * warp_u;
+        //      not written.  No CTA-wide copy-out phase. ----
+        const int wq_u = __shfl_sync(0xffffffffu, wq, 0);  // provably warp-uniform
+        const int t_warp = t_first + 32 * wq_u;
         if (t_warp < p.t_max) {
-          if (t_row >= n_fr) tc_zero_row(out_row);  // padding is +0.0 (padded_batch, train.py:192-197)
-          tc::fence_async_smem();
-          __syncwarp();
-#if defined(TC_ABLATE_STORE)
-          if (false) {
-#else
-          if (tc::elect_one()) {
-#endif
-            tc::tma_store_3d(&out_map, sOut_s + 4 * kTcOutPitch * 32 * warp_u, 0, t_warp, b);
-            tc::bulk_commit();
-            issuer = true;
+          if (group == 1) {
+            if (t_row >= n_fr) tc_zero_row(out_row);  // padding is +0.0 (padded_batch, train.py:192-197)
+            tc::fence_async_smem();
+            __syncwarp();
+            if (tc::elect_one()) {
+              tc::tma_store_3d(&out_map, sOut_s + 4 * kTcOutPitch * 32 * wq_u, 0, t_warp, b);
+              tc::bulk_commit();
+              issuer = true;
+            }
           }
           pending = true;
         }
       } else {
-        tc::named_bar_sync(1, 128);  // staged (and masked) rows visible to the 4 epilogue warps
+        tc::named_bar_sync(9, 256);  // staged (and masked) rows visible to the 8 epilogue warps
         // ---- copy-out with delta / delta-delta: staged tile -> HBM, 128-bit, fully coalesced -----
         float* out_b = p.out + static_cast<int64_t>(b) * p.t_max * 240;
         int i = tid / 20, quad = tid - 20 * i;
-        for (int it = 0; it < 20; ++it) {
+        for (int it = 0; it < 10; ++it) {
           const int t = t_first - tp.halo + i;
           if (i >= tp.halo && t < p.t_max) {
             float4 x0 = make_float4(0.f, 0.f, 0.f, 0.f), x1 = x0, x2 = x0;
@@ -368,14 +369,14 @@ __global__ void __launch_bounds__(kTcThreads, 1)
             o[1] = make_float4(dy, dy - ey, x0.z, dz);
             o[2] = make_float4(dz - ez, x0.w, dw, dw - ew);
           }
-          quad += 8;
-          i += 6;
+          quad += 16;
+          i += 12;
           if (quad >= 20) {
             quad -= 20;
             i += 1;
           }
         }
-        tc::named_bar_sync(1, 128);  // the staging tile may be overwritten
+        tc::named_bar_sync(9, 256);  // the staging tile may be overwritten
       }
     }
     if (C == 1 && issuer) tc::bulk_wait_all();
@@ -384,7 +385,7 @@ __global__ void __launch_bounds__(kTcThreads, 1)
   if (timed_out && p.status) atomicOr(p.status, 0x100);
   tc::tc_fence_before();
   __syncthreads();
-  if (warp == 8) tc::tmem_dealloc(tmem_base, 512);
+  if (warp == kTcMmaWarp) tc::tmem_dealloc(tmem_base, 512);
 }
 
 // cuTensorMapEncodeTiled through the runtime's driver entry point (no link-time libcuda dependency).
