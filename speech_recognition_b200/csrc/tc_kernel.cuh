@@ -47,12 +47,13 @@ constexpr int kTcSmemOut = kTcSmemA + 10 * kTcStreamBytes;     // 168960
 constexpr int kTcOutPitch = 84;                                // floats per staged row (16-B aligned, conflict-free)
 constexpr int kTcSmemCtl = kTcSmemOut + kTcTileM * kTcOutPitch * 4;  // 211968
 constexpr int kTcSmemTotal = kTcSmemCtl + 256 + 1024;          // + control block + alignment slack
-// Four warpgroups: epilogue groups A and B (warps 0-3, 4-7), producers (8-11), MMA issuer (warp 12;
-// 13-15 idle).  The launch allocates 128 registers per thread; setmaxnreg moves the idle warpgroup's
-// share to the others (per SM sub-partition: 2 x 168 + 136 + 40 = 512).
+// Four warpgroups: epilogue groups A and B (warps 0-3, 4-7), producers (warps 8-14), MMA issuer
+// (warp 15).  The launch allocates 128 registers per thread; setmaxnreg moves the producers' spare
+// registers to the epilogue (per SM sub-partition: 2 x 168 + 2 x 88 = 512).
 constexpr int kTcThreads = 512;
-constexpr int kTcMmaWarp = 12;
-constexpr int kTcRegsEpilogue = 168, kTcRegsProducer = 136, kTcRegsMma = 40;
+constexpr int kTcMmaWarp = 15;
+constexpr int kTcProducerThreads = 224;
+constexpr int kTcRegsEpilogue = 168, kTcRegsProducer = 88;
 constexpr int kTcBScaleLog2 = 10;          // B is stored as 2^10 * w * twiddle
 // power = |Y|^2 * 2^(-2*10) (B scale) * 2^(-30) (int16 -> [-1, 1) twice)
 #define TC_PSCALE 0x1p-50f

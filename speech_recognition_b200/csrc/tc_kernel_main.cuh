@@ -59,7 +59,7 @@ __device__ __noinline__ void tc_zero_row(float* row) {
 // producer, one group at a time.  Rare path, kept out of line.
 __device__ __noinline__ void tc_produce_tile_slow(const short* __restrict__ pcm, int64_t s_begin, int32_t len,
                                                   uint8_t* sA, int ptid) {
-  for (int g = ptid; g < 516; g += 128) {
+  for (int g = ptid; g < 516; g += kTcProducerThreads) {
     uint4 raw[5];
 #pragma unroll
     for (int q = 0; q < 5; ++q) raw[q] = tc_load8_slow(pcm, s_begin + 40 * g + 8 * q, len);
@@ -88,7 +88,7 @@ __global__ void __launch_bounds__(kTcThreads, 1)
   }
   if (tid == 0) {
     for (int r = 0; r < 5; ++r) {
-      tc::mbar_init(&ctl->a_full[r], 128);
+      tc::mbar_init(&ctl->a_full[r], kTcProducerThreads);
       tc::mbar_init(&ctl->a_empty[r], 1);
     }
     tc::mbar_init(&ctl->acc_full, 1);
@@ -104,18 +104,20 @@ __global__ void __launch_bounds__(kTcThreads, 1)
   const uint32_t tmem_base = ctl->tmem_base;
   bool timed_out = false;
 
-  if (warp >= 8 && warp < 12) {
-    // ======================= PRODUCERS (warps 8-11) =============================================
-    tc::setmaxnreg_inc<kTcRegsProducer>();
-    const int ptid = tid - 256;
+  if (warp >= 8 && warp != kTcMmaWarp) {
+    // ======================= PRODUCERS (warps 8-14: 224 threads) ================================
+    tc::setmaxnreg_dec<kTcRegsProducer>();
     // The streams of residue r are refilled as soon as the MMAs of residue r of the previous tile
     // have completed (a_empty[r]), while the tensor core is still busy with residues r+1..4: the
     // conversion work of tile n+1 overlaps the MMAs of tile n although there is one A stage only.
+    const int ptid = tid - 256;
     uint32_t n = 0;  // active tiles processed so far by this CTA
-    uint32_t ph[4];
+    // 516 groups of 40 samples = 129 hops (128 frames + the half-row of overlap): groups ptid and
+    // ptid + 224 for every thread, ptid + 448 for the first 68
+    const bool third = ptid < 516 - 2 * kTcProducerThreads;
+    uint32_t ph[3];
 #pragma unroll
-    for (int i = 0; i < 4; ++i) ph[i] = tc_stream_offset(ptid + 128 * i);
-    const uint32_t pht = tc_stream_offset(ptid + 512);
+    for (int i = 0; i < 3; ++i) ph[i] = tc_stream_offset(ptid + kTcProducerThreads * i);
     for (int tile = blockIdx.x; tile < tp.total_tiles; tile += gridDim.x) {
       const int b = tile / tp.tiles_per_utt, j = tile - b * tp.tiles_per_utt;
       const int32_t len = p.lengths[b];
@@ -126,38 +128,31 @@ __global__ void __launch_bounds__(kTcThreads, 1)
       const int32_t s_begin = 160 * (j * tp.tout - tp.halo);
       const uint32_t par = (n - 1) & 1;
       if ((reinterpret_cast<uintptr_t>(pcm) & 15) == 0) {
-        // 516 groups of 40 samples = 129 hops (128 frames + the half-row of overlap): four per thread,
-        // the last four by threads 0..3.  All global loads are issued before the first wait, so the
-        // DRAM latency overlaps the MMAs that are still reading the previous tile's streams.
+        // All global loads are issued before the first wait, so the DRAM latency overlaps the MMAs
+        // that are still reading the previous tile's streams.
         // Every frame t < n_fr ends at a multiple of 8 samples <= len, so clamping the 8-sample
         // block index into [0, len/8 - 1] never changes a sample a valid frame uses; blocks outside
         // only feed rows that the epilogue zero-fills (t >= n_fr) or drops (t < 0).
         const uint4* src = reinterpret_cast<const uint4*>(pcm);
         const int32_t blk_max = (len >> 3) - 1;  // n_fr >= 1 here, so len >= 320
-        uint32_t w[4][20], wt[20];
+        uint32_t w[3][20];
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          uint4 raw[5];
+        for (int i = 0; i < 3; ++i) {
+          if (i < 2 || third) {
+            uint4 raw[5];
 #pragma unroll
-          for (int q = 0; q < 5; ++q) {
-            const int32_t blk = (s_begin >> 3) + 5 * (ptid + 128 * i) + q;
-            raw[q] = __ldg(src + min(max(blk, 0), blk_max));
+            for (int q = 0; q < 5; ++q) {
+              const int32_t blk = (s_begin >> 3) + 5 * (ptid + kTcProducerThreads * i) + q;
+              raw[q] = __ldg(src + min(max(blk, 0), blk_max));
+            }
+            tc_xor_words(raw, w[i]);
           }
-          tc_xor_words(raw, w[i]);
-        }
-        if (ptid < 4) {
-          uint4 raw[5];
-#pragma unroll
-          for (int q = 0; q < 5; ++q) {
-            const int32_t blk = (s_begin >> 3) + 5 * (ptid + 512) + q;
-            raw[q] = __ldg(src + min(max(blk, 0), blk_max));
-          }
-          tc_xor_words(raw, wt);
         }
 #define TC_PRODUCE_RES(R)                                                                              \
   if (n > 0 && !timed_out && !tc::mbar_wait(&ctl->a_empty[R], par)) timed_out = true;                  \
-  _Pragma("unroll") for (int i = 0; i < 4; ++i) tc_produce_res<R>(w[i], sA, ph[i]);                    \
-  if (ptid < 4) tc_produce_res<R>(wt, sA, pht);                                                        \
+  tc_produce_res<R>(w[0], sA, ph[0]);                                                                  \
+  tc_produce_res<R>(w[1], sA, ph[1]);                                                                  \
+  if (third) tc_produce_res<R>(w[2], sA, ph[2]);                                                       \
   tc::fence_async_smem(); /* generic-proxy writes -> visible to the tensor core (async proxy) */       \
   tc::mbar_arrive(&ctl->a_full[R]);
         TC_PRODUCE_RES(0)
@@ -175,9 +170,9 @@ __global__ void __launch_bounds__(kTcThreads, 1)
       }
       ++n;
     }
-  } else if (warp >= 12) {
-    // ======================= MMA ISSUER (one thread of warp 12; warps 13-15 idle) ===============
-    tc::setmaxnreg_dec<kTcRegsMma>();
+  } else if (warp == kTcMmaWarp) {
+    // ======================= MMA ISSUER (one thread of warp 15) =================================
+    tc::setmaxnreg_dec<kTcRegsProducer>();
     if (warp == kTcMmaWarp && lane == 0) {
       uint32_t n = 0;
       const uint32_t idesc = tc::make_idesc_f16(128, 64);
