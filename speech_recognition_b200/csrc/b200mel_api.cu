@@ -237,6 +237,13 @@ int b200mel_mel_weights(const b200mel_handle* h, float* out_host) {
   return B200MEL_OK;
 }
 
+#if defined(TC_TRACE) && defined(B200MEL_WITH_TC)
+// developer-only (variant builds): copy the role trace of CTA 0 to the host
+int b200mel_debug_trace(long long* out_host) {
+  return cudaMemcpyFromSymbol(out_host, g_tc_trace, sizeof(g_tc_trace)) == cudaSuccess ? 0 : 3;
+}
+#endif
+
 int b200mel_tc_supported(const b200mel_handle* h) { return (h && h->tc_ok) ? 1 : 0; }
 
 int64_t b200mel_launch_count(const b200mel_handle* h) { return h ? h->launches.load() : 0; }

@@ -65,6 +65,9 @@ __device__ __forceinline__ void tc_produce_res(const uint32_t (&w)[20], uint8_t*
     const uint32_t d = tc::prmt(w[a >> 1], w[b >> 1], sel);
     tc_split_pair(d, hi[pi], lo[pi]);
   }
+#if defined(TC_ABLATE_PSTS)
+  if (ph != 0xFFFFFFFFu) return;  // (experiment: conversion work without the shared-memory stores)
+#endif
   *reinterpret_cast<uint4*>(sA + (0 * 5 + R) * kTcStreamBytes + ph) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
   *reinterpret_cast<uint4*>(sA + (1 * 5 + R) * kTcStreamBytes + ph) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
 }

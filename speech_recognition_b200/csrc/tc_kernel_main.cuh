@@ -67,6 +67,15 @@ __device__ __noinline__ void tc_produce_tile_slow(const short* __restrict__ pcm,
   }
 }
 
+#if defined(TC_TRACE)
+// developer trace (experiments/trace_roles.py): clock64 stamps of CTA 0, [role][tile][event]
+__device__ long long g_tc_trace[4][32][8];
+#define TC_STAMP(ROLE, N, EV)                                                   \
+  if (blockIdx.x == 0 && (N) < 32) g_tc_trace[ROLE][N][EV] = clock64();
+#else
+#define TC_STAMP(ROLE, N, EV)
+#endif
+
 template <int C>
 __global__ void __launch_bounds__(kTcThreads, 1)
     tc_frontend_kernel(const KernelParams p, const TcParams tp, const __grid_constant__ CUtensorMap out_map) {
@@ -104,13 +113,22 @@ __global__ void __launch_bounds__(kTcThreads, 1)
   const uint32_t tmem_base = ctl->tmem_base;
   bool timed_out = false;
 
+#if defined(TC_P6)
+  if (warp >= 8 && warp != kTcMmaWarp && warp != 11) {
+#else
   if (warp >= 8 && warp != kTcMmaWarp) {
+#endif
     // ======================= PRODUCERS (warps 8-14: 224 threads) ================================
     tc::setmaxnreg_dec<kTcRegsProducer>();
-    // The streams of residue r are refilled as soon as the MMAs of residue r of the previous tile
-    // have completed (a_empty[r]), while the tensor core is still busy with residues r+1..4: the
-    // conversion work of tile n+1 overlaps the MMAs of tile n although there is one A stage only.
+    // One A stage, refilled in two phases: the streams of residues 0-2 as soon as the previous tile's
+    // MMAs of those residues have completed, residues 3-4 after the rest (those MMAs wait for the
+    // epilogue to release TMEM).  The raw PCM of the NEXT tile is loaded into the same registers at
+    // the end of the tile, and its range was pulled into L2 one tile earlier.
+#if defined(TC_P6)
+    const int ptid = (warp < 11 ? warp - 8 : warp - 9) * 32 + lane;
+#else
     const int ptid = tid - 256;
+#endif
     uint32_t n = 0;  // active tiles processed so far by this CTA
     // 516 groups of 40 samples = 129 hops (128 frames + the half-row of overlap): groups ptid and
     // ptid + 224 for every thread, ptid + 448 for the first 68
@@ -118,91 +136,192 @@ __global__ void __launch_bounds__(kTcThreads, 1)
     uint32_t ph[3];
 #pragma unroll
     for (int i = 0; i < 3; ++i) ph[i] = tc_stream_offset(ptid + kTcProducerThreads * i);
+    // (length, offset) of the utterances of this CTA's next two tiles, fetched ahead of use.  Offsets
+    // are kept in 8-sample blocks (bit 31 = "not 16-byte aligned": such utterances take the slow path).
+    const bool pcm_al = (reinterpret_cast<uintptr_t>(p.pcm) & 15) == 0;
+    auto fetch_len = [&](int t) -> int32_t { return t < tp.total_tiles ? __ldg(p.lengths + t / tp.tiles_per_utt) : 0; };
+    auto fetch_blk = [&](int t) -> uint32_t {
+      if (t >= tp.total_tiles) return 0x80000000u;
+      const int bt = t / tp.tiles_per_utt;
+      const int64_t o = p.offsets ? __ldg(p.offsets + bt) : static_cast<int64_t>(bt) * p.row_stride;
+      return (pcm_al && (o & 7) == 0) ? static_cast<uint32_t>(o >> 3) : 0x80000000u;
+    };
+    int32_t len1 = fetch_len(blockIdx.x), len2 = fetch_len(blockIdx.x + gridDim.x);
+    uint32_t bb1 = fetch_blk(blockIdx.x), bb2 = fetch_blk(blockIdx.x + gridDim.x);
+    const uint4* pcm16 = reinterpret_cast<const uint4*>(p.pcm);
+    uint32_t w[3][20];  // this thread's groups: raw words (two samples each), XOR-ed in place before use
+    bool preloaded = false;
+    // raw words of one tile -> w: absolute 8-sample block index, clamped into the utterance
+#define TC_LOAD_GROUP(I, BLK0, BLO, BHI)                                                               \
+  _Pragma("unroll") for (int q = 0; q < 5; ++q) {                                                      \
+    const int32_t blk = (BLK0) + 5 * (ptid + kTcProducerThreads * (I)) + q;                            \
+    const uint4 v = __ldg(pcm16 + min(max(blk, (BLO)), (BHI)));                                        \
+    w[I][4 * q + 0] = v.x;                                                                             \
+    w[I][4 * q + 1] = v.y;                                                                             \
+    w[I][4 * q + 2] = v.z;                                                                             \
+    w[I][4 * q + 3] = v.w;                                                                             \
+  }
     for (int tile = blockIdx.x; tile < tp.total_tiles; tile += gridDim.x) {
       const int b = tile / tp.tiles_per_utt, j = tile - b * tp.tiles_per_utt;
-      const int32_t len = p.lengths[b];
+      const int32_t len = len1;
+      const uint32_t bb = bb1;
+      const int nx = tile + gridDim.x;  // next tile of this CTA: (len1, bb1) after the shift
+      len1 = len2;
+      bb1 = bb2;
+      len2 = fetch_len(nx + gridDim.x);
+      bb2 = fetch_blk(nx + gridDim.x);
+      // next tile: first block, clamp range (all in absolute 8-sample blocks; requires < 2^31 blocks)
+      const int jn = nx - (nx / tp.tiles_per_utt) * tp.tiles_per_utt;
+      const bool next_ok = !(bb1 & 0x80000000u) && jn * tp.tout < frames_of(len1, 320, 160);
+      const int32_t nb_lo = static_cast<int32_t>(bb1), nb_hi = nb_lo + (len1 >> 3) - 1;
+      const int32_t nb_0 = nb_lo + 20 * (jn * tp.tout - tp.halo);
+      if (next_ok && ptid == kTcProducerThreads - 1) {
+        // ask the TMA engine to pull the next tile's PCM range into L2
+        const int32_t q0 = nb_0 < nb_lo ? nb_lo : nb_0;
+        const int32_t q1 = nb_0 + 129 * 20 - 1 < nb_hi ? nb_0 + 129 * 20 - 1 : nb_hi;
+        if (q1 >= q0) tc::prefetch_l2(pcm16 + q0, 16u * (q1 - q0 + 1));
+      }
       const int n_fr = frames_of(len, 320, 160);
-      if (j * tp.tout >= n_fr) continue;  // nothing but padding: the epilogue zero-fills
-      const int64_t base = p.offsets ? p.offsets[b] : static_cast<int64_t>(b) * p.row_stride;
-      const short* pcm = reinterpret_cast<const short*>(p.pcm) + base;
+      if (j * tp.tout >= n_fr) {  // nothing but padding: the epilogue zero-fills
+        preloaded = false;
+        continue;
+      }
       const int32_t s_begin = 160 * (j * tp.tout - tp.halo);
       const uint32_t par = (n - 1) & 1;
-      if ((reinterpret_cast<uintptr_t>(pcm) & 15) == 0) {
-        // All global loads are issued before the first wait, so the DRAM latency overlaps the MMAs
-        // that are still reading the previous tile's streams.
+      if (!(bb & 0x80000000u)) {
         // Every frame t < n_fr ends at a multiple of 8 samples <= len, so clamping the 8-sample
         // block index into [0, len/8 - 1] never changes a sample a valid frame uses; blocks outside
         // only feed rows that the epilogue zero-fills (t >= n_fr) or drops (t < 0).
-        const uint4* src = reinterpret_cast<const uint4*>(pcm);
-        const int32_t blk_max = (len >> 3) - 1;  // n_fr >= 1 here, so len >= 320
-        uint32_t w[3][20];
-#pragma unroll
-        for (int i = 0; i < 3; ++i) {
-          if (i < 2 || third) {
-            uint4 raw[5];
-#pragma unroll
-            for (int q = 0; q < 5; ++q) {
-              const int32_t blk = (s_begin >> 3) + 5 * (ptid + kTcProducerThreads * i) + q;
-              raw[q] = __ldg(src + min(max(blk, 0), blk_max));
-            }
-            tc_xor_words(raw, w[i]);
-          }
+        if (ptid == 0) { TC_STAMP(0, n, 0) }
+        if (!preloaded) {
+          const int32_t b_lo = static_cast<int32_t>(bb), b_hi = b_lo + (len >> 3) - 1;  // n_fr >= 1: len >= 320
+          const int32_t b_0 = b_lo + (s_begin >> 3);
+          TC_LOAD_GROUP(0, b_0, b_lo, b_hi)
+          TC_LOAD_GROUP(1, b_0, b_lo, b_hi)
+          if (third) { TC_LOAD_GROUP(2, b_0, b_lo, b_hi) }
         }
-#define TC_PRODUCE_RES(R)                                                                              \
-  if (n > 0 && !timed_out && !tc::mbar_wait(&ctl->a_empty[R], par)) timed_out = true;                  \
-  tc_produce_res<R>(w[0], sA, ph[0]);                                                                  \
-  tc_produce_res<R>(w[1], sA, ph[1]);                                                                  \
-  if (third) tc_produce_res<R>(w[2], sA, ph[2]);                                                       \
-  tc::fence_async_smem(); /* generic-proxy writes -> visible to the tensor core (async proxy) */       \
-  tc::mbar_arrive(&ctl->a_full[R]);
-        TC_PRODUCE_RES(0)
-        TC_PRODUCE_RES(1)
-        TC_PRODUCE_RES(2)
-        TC_PRODUCE_RES(3)
-        TC_PRODUCE_RES(4)
-#undef TC_PRODUCE_RES
+#pragma unroll
+        for (int i = 0; i < 3; ++i)
+#pragma unroll
+          for (int k = 0; k < 20; ++k) w[i][k] ^= 0x80008000u;
+        if (ptid == 0) { TC_STAMP(0, n, 1) }
+        // ---- phase 1: residues 0-2
+        if (n > 0 && !timed_out) {
+          if (!tc::mbar_wait(&ctl->a_empty[0], par) || !tc::mbar_wait(&ctl->a_empty[1], par) ||
+              !tc::mbar_wait(&ctl->a_empty[2], par))
+            timed_out = true;
+        }
+        if (ptid == 0) { TC_STAMP(0, n, 2) }
+        tc_produce_res<0>(w[0], sA, ph[0]);
+        tc_produce_res<1>(w[0], sA, ph[0]);
+        tc_produce_res<2>(w[0], sA, ph[0]);
+        tc_produce_res<0>(w[1], sA, ph[1]);
+        tc_produce_res<1>(w[1], sA, ph[1]);
+        tc_produce_res<2>(w[1], sA, ph[1]);
+        if (third) {
+          tc_produce_res<0>(w[2], sA, ph[2]);
+          tc_produce_res<1>(w[2], sA, ph[2]);
+          tc_produce_res<2>(w[2], sA, ph[2]);
+        }
+        tc::fence_async_smem();  // generic-proxy writes -> visible to the tensor core (async proxy)
+        tc::mbar_arrive(&ctl->a_full[0]);
+        tc::mbar_arrive(&ctl->a_full[1]);
+        tc::mbar_arrive(&ctl->a_full[2]);
+        if (ptid == 0) { TC_STAMP(0, n, 3) }
+        // ---- phase 2: residues 3-4, then reload the registers with the next tile's PCM
+        if (n > 0 && !timed_out) {
+          if (!tc::mbar_wait(&ctl->a_empty[3], par) || !tc::mbar_wait(&ctl->a_empty[4], par)) timed_out = true;
+        }
+        if (ptid == 0) { TC_STAMP(0, n, 4) }
+        tc_produce_res<3>(w[0], sA, ph[0]);
+        tc_produce_res<4>(w[0], sA, ph[0]);
+        tc_produce_res<3>(w[1], sA, ph[1]);
+        tc_produce_res<4>(w[1], sA, ph[1]);
+        if (third) {
+          tc_produce_res<3>(w[2], sA, ph[2]);
+          tc_produce_res<4>(w[2], sA, ph[2]);
+        }
+        tc::fence_async_smem();
+        tc::mbar_arrive(&ctl->a_full[3]);
+        tc::mbar_arrive(&ctl->a_full[4]);
+        // the registers are free: start loading the next tile's PCM (its range is in L2 by now).
+        // After the fence on purpose - the fence waits for this thread's outstanding loads.
+        if (next_ok) {
+          TC_LOAD_GROUP(0, nb_0, nb_lo, nb_hi)
+          TC_LOAD_GROUP(1, nb_0, nb_lo, nb_hi)
+          if (third) { TC_LOAD_GROUP(2, nb_0, nb_lo, nb_hi) }
+        }
+        preloaded = next_ok;
+        if (ptid == 0) { TC_STAMP(0, n, 6) }
       } else {
         for (int r = 0; r < 5; ++r)
           if (n > 0 && !timed_out && !tc::mbar_wait(&ctl->a_empty[r], par)) timed_out = true;
-        tc_produce_tile_slow(pcm, s_begin, len, sA, ptid);
+        const int64_t base = p.offsets ? p.offsets[b] : static_cast<int64_t>(b) * p.row_stride;
+        tc_produce_tile_slow(reinterpret_cast<const short*>(p.pcm) + base, s_begin, len, sA, ptid);
         tc::fence_async_smem();
         for (int r = 0; r < 5; ++r) tc::mbar_arrive(&ctl->a_full[r]);
+        preloaded = false;
       }
       ++n;
     }
-  } else if (warp == kTcMmaWarp) {
+#undef TC_LOAD_GROUP
+  } else if (warp >= 8) {
     // ======================= MMA ISSUER (one thread of warp 15) =================================
     tc::setmaxnreg_dec<kTcRegsProducer>();
-    if (warp == kTcMmaWarp && lane == 0) {
+    if (warp == kTcMmaWarp && tc::elect_one()) {
       uint32_t n = 0;
       const uint32_t idesc = tc::make_idesc_f16(128, 64);
       const uint64_t a_base = tc::make_smem_desc(tc::smem_u32(sA), 16, 512, tc::kLayoutSw64);
       const uint64_t b_base = tc::make_smem_desc(tc::smem_u32(sB), 16, 1024, tc::kLayoutSw128);
+      const uint32_t a_lo0 = static_cast<uint32_t>(a_base), a_hi = static_cast<uint32_t>(a_base >> 32);
+      const uint32_t b_lo0 = static_cast<uint32_t>(b_base), b_hi = static_cast<uint32_t>(b_base >> 32);
+      // "is this tile active" is evaluated one tile ahead, while the tensor pipe is busy with queued
+      // MMAs, so that the issuing thread has nothing to do between two tiles
+      auto tile_len = [&](int t) -> int32_t { return t < tp.total_tiles ? __ldg(p.lengths + t / tp.tiles_per_utt) : 0; };
+      auto tile_active = [&](int t, int32_t len_t) -> bool {
+        const int jt = t - (t / tp.tiles_per_utt) * tp.tiles_per_utt;
+        return t < tp.total_tiles && jt * tp.tout < frames_of(len_t, 320, 160);
+      };
+      bool cur_active = tile_active(blockIdx.x, tile_len(blockIdx.x));
       for (int tile = blockIdx.x; tile < tp.total_tiles; tile += gridDim.x) {
-        const int b = tile / tp.tiles_per_utt, j = tile - b * tp.tiles_per_utt;
-        const int n_fr = frames_of(p.lengths[b], 320, 160);
-        if (j * tp.tout >= n_fr) continue;
+        const int nx = tile + gridDim.x;
+        if (!cur_active) {
+          cur_active = tile_active(nx, tile_len(nx));
+          continue;
+        }
+        const int32_t len_n = tile_len(nx);  // consumed after the MMAs of residue 2 are queued
+        bool nxt_active = false;
 #pragma unroll 1
         for (int r = 0; r < 5; ++r) {
+          if (r == 0) { TC_STAMP(1, n, 0) }
           if (!timed_out && !tc::mbar_wait(&ctl->a_full[r], n & 1)) timed_out = true;
+          if (r == 0) { TC_STAMP(1, n, 1) }
+          if (r == 3) { TC_STAMP(1, n, 2) }
           // slots of residues 3, 4 were residues 0, 1 of the previous tile: wait for its epilogue
           if (r == 3 && n > 0 && !timed_out && !tc::mbar_wait(&ctl->acc_empty, (n - 1) & 1)) timed_out = true;
           tc::tc_fence_after();
+          if (r == 3) { TC_STAMP(1, n, 3) }
           const uint32_t d_tmem = tmem_base + (((5u * n + r) & 7u) << 6);
-          // passes, smallest magnitude first: lo x Bhi, hi x Blo, hi x Bhi
+          // passes, smallest magnitude first: lo x Bhi, hi x Blo, hi x Bhi; descriptor offsets in
+          // 16-byte units: stream (term, r) at (5 term + r) * 544, matrix (term, r) at (5 term + r) * 512
+          const uint32_t a_r = a_lo0 + 544u * r, b_r = b_lo0 + 512u * r;
 #pragma unroll
           for (int ps = 0; ps < 3; ++ps) {
-            const int a_term = ps == 0 ? 1 : 0, b_term = ps == 1 ? 1 : 0;
+            const uint32_t a_t = ps == 0 ? 5u * 544u : 0u, b_t = ps == 1 ? 5u * 512u : 0u;
 #pragma unroll
             for (int ks = 0; ks < 4; ++ks) {
-              const uint32_t a_off = (a_term * 5 + r) * kTcStreamBytes + 32 * ks;
-              const uint32_t b_off = (b_term * 5 + r) * kTcBBytes + 32 * ks;
-              tc::umma_f16(d_tmem, a_base + (a_off >> 4), b_base + (b_off >> 4), idesc, (ps | ks) ? 1u : 0u);
+              if (ps == 0 && ks == 0)
+                tc::umma_f16<false>(d_tmem, a_r + a_t + 2u * ks, a_hi, b_r + b_t + 2u * ks, b_hi, idesc);
+              else
+                tc::umma_f16<true>(d_tmem, a_r + a_t + 2u * ks, a_hi, b_r + b_t + 2u * ks, b_hi, idesc);
             }
           }
           tc::umma_commit(&ctl->a_empty[r]);  // residue r's streams may be refilled
+          if (r == 2) nxt_active = tile_active(nx, len_n);
         }
         tc::umma_commit(&ctl->acc_full);
+        TC_STAMP(1, n, 4)
+        cur_active = nxt_active;
         ++n;
       }
     }
@@ -226,28 +345,37 @@ __global__ void __launch_bounds__(kTcThreads, 1)
     const uint32_t bar_ready = 1 + wq, bar_free = 5 + wq;  // pair barriers (64 threads)
     bool pending = false;  // C == 1: the pair's previous TMA store may still be reading the staged rows
     bool issuer = false;   // this thread issued it (bulk async-groups are per thread)
+    int32_t len_nxt = blockIdx.x < tp.total_tiles ? __ldg(p.lengths + blockIdx.x / tp.tiles_per_utt) : 0;
     for (int tile = blockIdx.x; tile < tp.total_tiles; tile += gridDim.x) {
       const int b = tile / tp.tiles_per_utt, j = tile - b * tp.tiles_per_utt;
-      const int32_t len = p.lengths[b];
+      const int32_t len = len_nxt;  // fetched one tile ahead
+      {
+        const int nx = tile + gridDim.x;
+        if (nx < tp.total_tiles) len_nxt = __ldg(p.lengths + nx / tp.tiles_per_utt);
+      }
       const int n_fr = frames_of(len, 320, 160);
       const int t_first = j * tp.tout;  // first OUTPUT frame of this tile; row i holds frame t_first - halo + i
       const bool active = t_first < n_fr;
       const int t_row = t_first - tp.halo + row;
       if (tid == 0 && j == 0 && p.n_frames) p.n_frames[b] = n_fr;
+      // C == 1: the staged rows are free once the pair's previous TMA store has read them.  B waits
+      // for that read and tells A, which only needs it before its first write to the rows.
+      bool need_free = false;
       if (C == 1 && pending) {
-        // B: the staged rows are free once the previous store has read them; A waits for that
         if (group == 1) {
           if (issuer) tc::bulk_wait_read();
           __syncwarp();
           tc::named_bar_arrive(bar_free, 64);
         } else {
-          tc::named_bar_sync(bar_free, 64);
+          need_free = true;
         }
         pending = false;
       }
       if (active) {
+        if (lane == 0 && wq == 0) { TC_STAMP(2 + group, n, 0) }
         if (!timed_out && !tc::mbar_wait(&ctl->acc_full, n & 1)) timed_out = true;
         tc::tc_fence_after();
+        if (lane == 0 && wq == 0) { TC_STAMP(2 + group, n, 1) }
         TC_DECL_ACC
         float P[20], Q[6], d[5][8];
         const uint32_t t_tile = tmem_base + lane_base;
@@ -269,6 +397,7 @@ __global__ void __launch_bounds__(kTcThreads, 1)
     /* this thread's TMEM reads of the tile are done: hand the slots back before the arithmetic */ \
     tc::tc_fence_before();                                                                        \
     tc::mbar_arrive(&ctl->acc_empty);                                                             \
+    if (lane == 0 && wq == 0) { TC_STAMP(2 + group, n, 2) }                                       \
   }
         // both groups run the SAME loop code (instruction-cache footprint): group A chunks 0-3, B 4-7
         const int c0 = 4 * group;
@@ -298,6 +427,10 @@ __global__ void __launch_bounds__(kTcThreads, 1)
           TC_RADIX_STEP(1)
           TC_RADIX_STEP(2)
           TC_RADIX_STEP(3)
+          if (need_free) {
+            tc::named_bar_sync(bar_free, 64);
+            need_free = false;
+          }
           switch (c) {
             case 0: TC_MEL_CHUNK_0(Q, P); break;
             case 1: TC_MEL_CHUNK_1(Q, P); break;
@@ -309,9 +442,11 @@ __global__ void __launch_bounds__(kTcThreads, 1)
             default: TC_MEL_CHUNK_7(Q, P); break;
           }
         }
+        if (lane == 0 && wq == 0) { TC_STAMP(2 + group, n, 3) }
         if (group == 1) {
           // A's finished bins and parked partial sums of this row are in shared memory
           tc::named_bar_sync(bar_ready, 64);
+          if (lane == 0 && wq == 0) { TC_STAMP(3, n, 4) }
           TC_MEL_SHARED_B;
           if (n_masks > 0 && t_row >= 0 && t_row < n_fr)
             tc_mask_row(out_row, p.mask_table + static_cast<size_t>(b) * 2 * n_masks, p.n_masks_f, p.n_masks_t, t_row);
@@ -319,8 +454,10 @@ __global__ void __launch_bounds__(kTcThreads, 1)
 #undef TC_LOAD_CHUNK
 #undef TC_RADIX_STEP
         if (group == 0) tc::named_bar_arrive(bar_ready, 64);
+        if (lane == 0 && wq == 0) { TC_STAMP(2 + group, n, 5) }
         ++n;
       }
+      if (need_free) tc::named_bar_sync(bar_free, 64);  // (tile of padding only: keep the barrier phases paired)
 
       if (C == 1) {
         // ---- group B stores the pair's 32 staged rows with ONE TMA tensor store: the box is

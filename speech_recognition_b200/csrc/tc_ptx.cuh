@@ -27,11 +27,21 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
   return ok != 0;
 }
 // Bounded wait: a protocol bug must never hang the GPU.  Returns false on timeout.
+// (try_wait may suspend the thread for a while inside one poll, so bound by time, not by polls)
 __device__ __forceinline__ bool mbar_wait(uint64_t* bar, uint32_t parity) {
-  // (try_wait may suspend the thread for a while inside one poll, so bound by time, not by polls)
   const long long t0 = clock64();
   while (!mbar_try_wait(bar, parity))
     if (clock64() - t0 > 200000000LL) return false;  // ~0.1 s
+  return true;
+}
+// Same for a role with slack (the producers): sleep between polls, so that waiting warps do not burn
+// the issue slots the epilogue warps of the same SM sub-partition need.
+__device__ __forceinline__ bool mbar_wait_relaxed(uint64_t* bar, uint32_t parity) {
+  const long long t0 = clock64();
+  while (!mbar_try_wait(bar, parity)) {
+    __nanosleep(200);
+    if (clock64() - t0 > 200000000LL) return false;
+  }
   return true;
 }
 
@@ -53,11 +63,17 @@ __host__ __device__ constexpr uint32_t make_idesc_f16(int M, int N) {
   return (1u << 4) | (static_cast<uint32_t>(N >> 3) << 17) | (static_cast<uint32_t>(M >> 4) << 24);
 }
 
-__device__ __forceinline__ void umma_f16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+// Descriptors are passed as (lo, hi) words: the per-MMA offset only touches the low word (14-bit
+// start-address field), so the issuing thread spends one 32-bit add per operand.
+template <bool kAccumulate>
+__device__ __forceinline__ void umma_f16(uint32_t d_tmem, uint32_t a_lo, uint32_t a_hi, uint32_t b_lo, uint32_t b_hi,
+                                         uint32_t idesc) {
   asm volatile(
-      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
-      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
-      ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+      "{\n\t.reg .b64 da, db;\n\t.reg .pred p;\n\t"
+      "mov.b64 da, {%1, %2};\n\tmov.b64 db, {%3, %4};\n\t"
+      "setp.ne.b32 p, %6, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %5, p;\n\t}"
+      ::"r"(d_tmem), "r"(a_lo), "r"(a_hi), "r"(b_lo), "r"(b_hi), "r"(idesc), "n"(kAccumulate ? 1 : 0)
       : "memory");
 }
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
@@ -111,6 +127,10 @@ __device__ __forceinline__ void tma_store_3d(const void* tmap, uint32_t ssrc, in
   asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%1, %2, %3}], [%4];" ::"l"(tmap), "r"(c0),
                "r"(c1), "r"(c2), "r"(ssrc)
                : "memory");
+}
+// Asynchronous prefetch of a global range into L2 (addr 16-byte aligned, size a multiple of 16).
+__device__ __forceinline__ void prefetch_l2(const void* gsrc, uint32_t bytes) {
+  asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(gsrc), "r"(bytes) : "memory");
 }
 // true in exactly one (elected) lane of a converged warp
 __device__ __forceinline__ bool elect_one() {
