@@ -47,16 +47,12 @@ constexpr int kTcSmemOut = kTcSmemA + 10 * kTcStreamBytes;     // 168960
 constexpr int kTcOutPitch = 84;                                // floats per staged row (16-B aligned, conflict-free)
 constexpr int kTcSmemCtl = kTcSmemOut + kTcTileM * kTcOutPitch * 4;  // 211968
 constexpr int kTcSmemTotal = kTcSmemCtl + 256 + 1024;          // + control block + alignment slack
-// Four warpgroups: epilogue groups A and B (warps 0-3, 4-7), producers (warps 8-14), MMA issuer
-// (warp 15).  The launch allocates 128 registers per thread; setmaxnreg moves the producers' spare
-// registers to the epilogue (per SM sub-partition: 2 x 160 + 2 x 96 = 512).
+// Four warpgroups: MMA issuer (warp 0) + producers (warps 1-7), epilogue groups A and B (warps 8-11,
+// 12-15).  The launch allocates 128 registers per thread; setmaxnreg moves the producers' spare
+// registers to the epilogue (per SM sub-partition: 2 x 96 + 2 x 160 = 512).
 constexpr int kTcThreads = 512;
-constexpr int kTcMmaWarp = 15;
-#if defined(TC_P6)
-constexpr int kTcProducerThreads = 192;  // (experiment: warp 11 idle, the MMA warp's sub-partition hosts no producer)
-#else
+constexpr int kTcMmaWarp = 0;
 constexpr int kTcProducerThreads = 224;
-#endif
 constexpr int kTcRegsEpilogue = 160, kTcRegsProducer = 96;
 constexpr int kTcBScaleLog2 = 10;          // B is stored as 2^10 * w * twiddle
 // power = |Y|^2 * 2^(-2*10) (B scale) * 2^(-30) (int16 -> [-1, 1) twice)

@@ -103,6 +103,64 @@ __device__ __noinline__ void tc_produce_group(uint4 r0, uint4 r1, uint4 r2, uint
 #define TC_S1 0.95105651629515357212f
 #define TC_S2 0.58778525229247312917f
 
+// Packed f32x2 arithmetic (sm_100: one instruction, two FP32 lanes): a complex value is one
+// (re, im) register pair, straight out of two adjacent TMEM columns.
+typedef unsigned long long tc_f2;
+__device__ __forceinline__ tc_f2 tc_pk(float a, float b) {
+  tc_f2 r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b));
+  return r;
+}
+__device__ __forceinline__ void tc_upk(tc_f2 v, float& a, float& b) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v));
+}
+__device__ __forceinline__ tc_f2 tc_add2(tc_f2 a, tc_f2 b) {
+  tc_f2 r;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+__device__ __forceinline__ tc_f2 tc_mul2(tc_f2 a, tc_f2 b) {
+  tc_f2 r;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+__device__ __forceinline__ tc_f2 tc_fma2(tc_f2 a, tc_f2 b, tc_f2 c) {
+  tc_f2 r;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+  return r;
+}
+
+// complex inputs x[r] = (re, im) pairs; outputs p[k2] = |sum_r W5^{r k2} x_r|^2.
+// |p + q|^2 and |p - q|^2 with q = -i t share E = |p|^2 + |t|^2 and differ by +-2 (p_r t_i - p_i t_r).
+__device__ __forceinline__ void tc_radix5_power2(const tc_f2* x, float& p0, float& p1, float& p2, float& p3, float& p4) {
+  const tc_f2 m1 = tc_pk(-1.0f, -1.0f);
+  const tc_f2 c1 = tc_pk(TC_C1, TC_C1), c2 = tc_pk(TC_C2, TC_C2), s1 = tc_pk(TC_S1, TC_S1), s2 = tc_pk(TC_S2, TC_S2);
+  const tc_f2 ns1 = tc_pk(-TC_S1, -TC_S1);
+  const tc_f2 a1 = tc_add2(x[1], x[4]), b1 = tc_fma2(x[4], m1, x[1]);
+  const tc_f2 a2 = tc_add2(x[2], x[3]), b2 = tc_fma2(x[3], m1, x[2]);
+  const tc_f2 x0 = tc_add2(x[0], tc_add2(a1, a2));
+  const tc_f2 q1 = tc_fma2(c2, a2, tc_fma2(c1, a1, x[0]));
+  const tc_f2 q2 = tc_fma2(c1, a2, tc_fma2(c2, a1, x[0]));
+  const tc_f2 t1 = tc_fma2(s2, b2, tc_mul2(s1, b1));
+  const tc_f2 t2 = tc_fma2(ns1, b2, tc_mul2(s2, b1));
+  float ar, ai;
+  tc_upk(tc_mul2(x0, x0), ar, ai);
+  p0 = ar + ai;
+  float e1a, e1b, e2a, e2b, q1r, q1i, q2r, q2i, t1r, t1i, t2r, t2i;
+  tc_upk(tc_fma2(t1, t1, tc_mul2(q1, q1)), e1a, e1b);
+  tc_upk(tc_fma2(t2, t2, tc_mul2(q2, q2)), e2a, e2b);
+  tc_upk(q1, q1r, q1i);
+  tc_upk(t1, t1r, t1i);
+  tc_upk(q2, q2r, q2i);
+  tc_upk(t2, t2r, t2i);
+  const float e1 = e1a + e1b, e2 = e2a + e2b;
+  const float x1 = fmaf(q1r, t1i, -(q1i * t1r)), x2 = fmaf(q2r, t2i, -(q2i * t2r));
+  p1 = fmaf(2.0f, x1, e1);
+  p4 = fmaf(-2.0f, x1, e1);
+  p2 = fmaf(2.0f, x2, e2);
+  p3 = fmaf(-2.0f, x2, e2);
+}
+
 // complex inputs (xr[r], xi[r]); outputs p[k2] = |sum_r W5^{r k2} x_r|^2
 __device__ __forceinline__ void tc_radix5_power(const float* xr, const float* xi, float& p0, float& p1, float& p2,
                                                 float& p3, float& p4) {

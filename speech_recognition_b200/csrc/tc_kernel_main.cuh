@@ -4,8 +4,9 @@
 namespace b200mel {
 
 struct TcCtl {
-  uint64_t a_full[5];   // producers (128 arrivals) -> MMA: streams (hi, lo) of residue r are in smem
-  uint64_t a_empty[5];  // tcgen05.commit -> producers: the MMAs that read residue r's streams are done
+  // the A stage is handed over in two phases: [0] = streams of residues 0-2, [1] = residues 3-4
+  uint64_t a_full[2];   // producers (224 arrivals) -> MMA: the phase's streams (hi, lo) are in smem
+  uint64_t a_empty[2];  // tcgen05.commit -> producers: the MMAs that read the phase's streams are done
   uint64_t acc_full;    // tcgen05.commit -> epilogue: the 5 accumulators of this tile are complete
   uint64_t acc_empty;   // epilogue (128 arrivals) -> MMA: this tile's TMEM slots may be overwritten
   uint32_t tmem_base;
@@ -19,14 +20,19 @@ __device__ __forceinline__ float tc_finish(float acc, float eps, float log_eps) 
   return acc == 0.0f ? log_eps : l2 * 0.69314718055994530942f;
 }
 
-#define TC_FINISH1(M_, A) out_row[M_] = tc_finish(A, eps, log_eps)
+#if defined(TC_ABLATE_ESTS)
+#define TC_ROW_ST(PTR, V) if (eps == 12345.0f) *(PTR) = (V) /* (experiment: no staging stores) */
+#else
+#define TC_ROW_ST(PTR, V) *(PTR) = (V)
+#endif
+#define TC_FINISH1(M_, A) TC_ROW_ST(out_row + (M_), tc_finish(A, eps, log_eps))
 // shared bins: group A parks its partial sum in the staged row, group B adds its own and finishes
-#define TC_PART1(M_, A) out_row[M_] = (A)
-#define TC_SHARED1(M_, A) out_row[M_] = tc_finish((A) + out_row[M_], eps, log_eps)
+#define TC_PART1(M_, A) TC_ROW_ST(out_row + (M_), (A))
+#define TC_SHARED1(M_, A) TC_ROW_ST(out_row + (M_), tc_finish((A) + out_row[M_], eps, log_eps))
 #define TC_FINISH4(G, A, B, C, D)                                                              \
-  *reinterpret_cast<float4*>(out_row + 4 * (G)) =                                              \
-      make_float4(tc_finish(A, eps, log_eps), tc_finish(B, eps, log_eps), tc_finish(C, eps, log_eps), \
-                  tc_finish(D, eps, log_eps))
+  TC_ROW_ST(reinterpret_cast<float4*>(out_row + 4 * (G)),                                      \
+            make_float4(tc_finish(A, eps, log_eps), tc_finish(B, eps, log_eps), tc_finish(C, eps, log_eps), \
+                        tc_finish(D, eps, log_eps)))
 
 // SpecAugment on the thread's own staged row (data.py:286-288, 299-301): audio *= mask, so a masked
 // negative value becomes -0.0 exactly like the reference's multiply.  tb = (start, width) pairs,
@@ -96,7 +102,7 @@ __global__ void __launch_bounds__(kTcThreads, 1)
     for (int i = tid; i < 10 * kTcBBytes / 16; i += kTcThreads) dst[i] = __ldg(src + i);
   }
   if (tid == 0) {
-    for (int r = 0; r < 5; ++r) {
+    for (int r = 0; r < 2; ++r) {
       tc::mbar_init(&ctl->a_full[r], kTcProducerThreads);
       tc::mbar_init(&ctl->a_empty[r], 1);
     }
@@ -113,22 +119,14 @@ __global__ void __launch_bounds__(kTcThreads, 1)
   const uint32_t tmem_base = ctl->tmem_base;
   bool timed_out = false;
 
-#if defined(TC_P6)
-  if (warp >= 8 && warp != kTcMmaWarp && warp != 11) {
-#else
-  if (warp >= 8 && warp != kTcMmaWarp) {
-#endif
-    // ======================= PRODUCERS (warps 8-14: 224 threads) ================================
+  if (warp >= 1 && warp < 8) {
+    // ======================= PRODUCERS (warps 1-7: 224 threads) =================================
     tc::setmaxnreg_dec<kTcRegsProducer>();
     // One A stage, refilled in two phases: the streams of residues 0-2 as soon as the previous tile's
     // MMAs of those residues have completed, residues 3-4 after the rest (those MMAs wait for the
     // epilogue to release TMEM).  The raw PCM of the NEXT tile is loaded into the same registers at
     // the end of the tile, and its range was pulled into L2 one tile earlier.
-#if defined(TC_P6)
-    const int ptid = (warp < 11 ? warp - 8 : warp - 9) * 32 + lane;
-#else
-    const int ptid = tid - 256;
-#endif
+    const int ptid = tid - 32;
     uint32_t n = 0;  // active tiles processed so far by this CTA
     // 516 groups of 40 samples = 129 hops (128 frames + the half-row of overlap): groups ptid and
     // ptid + 224 for every thread, ptid + 448 for the first 68
@@ -206,11 +204,7 @@ __global__ void __launch_bounds__(kTcThreads, 1)
           for (int k = 0; k < 20; ++k) w[i][k] ^= 0x80008000u;
         if (ptid == 0) { TC_STAMP(0, n, 1) }
         // ---- phase 1: residues 0-2
-        if (n > 0 && !timed_out) {
-          if (!tc::mbar_wait(&ctl->a_empty[0], par) || !tc::mbar_wait(&ctl->a_empty[1], par) ||
-              !tc::mbar_wait(&ctl->a_empty[2], par))
-            timed_out = true;
-        }
+        if (n > 0 && !timed_out && !tc::mbar_wait(&ctl->a_empty[0], par)) timed_out = true;
         if (ptid == 0) { TC_STAMP(0, n, 2) }
         tc_produce_res<0>(w[0], sA, ph[0]);
         tc_produce_res<1>(w[0], sA, ph[0]);
@@ -225,13 +219,9 @@ __global__ void __launch_bounds__(kTcThreads, 1)
         }
         tc::fence_async_smem();  // generic-proxy writes -> visible to the tensor core (async proxy)
         tc::mbar_arrive(&ctl->a_full[0]);
-        tc::mbar_arrive(&ctl->a_full[1]);
-        tc::mbar_arrive(&ctl->a_full[2]);
         if (ptid == 0) { TC_STAMP(0, n, 3) }
         // ---- phase 2: residues 3-4, then reload the registers with the next tile's PCM
-        if (n > 0 && !timed_out) {
-          if (!tc::mbar_wait(&ctl->a_empty[3], par) || !tc::mbar_wait(&ctl->a_empty[4], par)) timed_out = true;
-        }
+        if (n > 0 && !timed_out && !tc::mbar_wait(&ctl->a_empty[1], par)) timed_out = true;
         if (ptid == 0) { TC_STAMP(0, n, 4) }
         tc_produce_res<3>(w[0], sA, ph[0]);
         tc_produce_res<4>(w[0], sA, ph[0]);
@@ -242,8 +232,7 @@ __global__ void __launch_bounds__(kTcThreads, 1)
           tc_produce_res<4>(w[2], sA, ph[2]);
         }
         tc::fence_async_smem();
-        tc::mbar_arrive(&ctl->a_full[3]);
-        tc::mbar_arrive(&ctl->a_full[4]);
+        tc::mbar_arrive(&ctl->a_full[1]);
         // the registers are free: start loading the next tile's PCM (its range is in L2 by now).
         // After the fence on purpose - the fence waits for this thread's outstanding loads.
         if (next_ok) {
@@ -254,21 +243,24 @@ __global__ void __launch_bounds__(kTcThreads, 1)
         preloaded = next_ok;
         if (ptid == 0) { TC_STAMP(0, n, 6) }
       } else {
-        for (int r = 0; r < 5; ++r)
+        for (int r = 0; r < 2; ++r)
           if (n > 0 && !timed_out && !tc::mbar_wait(&ctl->a_empty[r], par)) timed_out = true;
         const int64_t base = p.offsets ? p.offsets[b] : static_cast<int64_t>(b) * p.row_stride;
         tc_produce_tile_slow(reinterpret_cast<const short*>(p.pcm) + base, s_begin, len, sA, ptid);
         tc::fence_async_smem();
-        for (int r = 0; r < 5; ++r) tc::mbar_arrive(&ctl->a_full[r]);
+        for (int r = 0; r < 2; ++r) tc::mbar_arrive(&ctl->a_full[r]);
         preloaded = false;
       }
       ++n;
     }
 #undef TC_LOAD_GROUP
-  } else if (warp >= 8) {
-    // ======================= MMA ISSUER (one thread of warp 15) =================================
+  } else if (warp == 0) {
+    // ======================= MMA ISSUER (one thread of warp 0) ==================================
+    // Warp 0 on purpose: the issuing thread needs an instruction slot every few cycles to keep the
+    // tensor pipe fed, and the warp schedulers favour the oldest (lowest) warp of a sub-partition -
+    // as the youngest warp it was starved by the epilogue warps (96 instead of 60 cycles per MMA).
     tc::setmaxnreg_dec<kTcRegsProducer>();
-    if (warp == kTcMmaWarp && tc::elect_one()) {
+    if (tc::elect_one()) {
       uint32_t n = 0;
       const uint32_t idesc = tc::make_idesc_f16(128, 64);
       const uint64_t a_base = tc::make_smem_desc(tc::smem_u32(sA), 16, 512, tc::kLayoutSw64);
@@ -293,13 +285,19 @@ __global__ void __launch_bounds__(kTcThreads, 1)
         bool nxt_active = false;
 #pragma unroll 1
         for (int r = 0; r < 5; ++r) {
-          if (r == 0) { TC_STAMP(1, n, 0) }
-          if (!timed_out && !tc::mbar_wait(&ctl->a_full[r], n & 1)) timed_out = true;
-          if (r == 0) { TC_STAMP(1, n, 1) }
-          if (r == 3) { TC_STAMP(1, n, 2) }
-          // slots of residues 3, 4 were residues 0, 1 of the previous tile: wait for its epilogue
-          if (r == 3 && n > 0 && !timed_out && !tc::mbar_wait(&ctl->acc_empty, (n - 1) & 1)) timed_out = true;
-          tc::tc_fence_after();
+          if (r == 0) {
+            TC_STAMP(1, n, 0)
+            if (!timed_out && !tc::mbar_wait(&ctl->a_full[0], n & 1)) timed_out = true;
+            tc::tc_fence_after();
+            TC_STAMP(1, n, 1)
+          }
+          if (r == 3) {
+            TC_STAMP(1, n, 2)
+            // slots of residues 3, 4 were residues 0, 1 of the previous tile: wait for its epilogue
+            if (!timed_out && !tc::mbar_wait(&ctl->a_full[1], n & 1)) timed_out = true;
+            if (n > 0 && !timed_out && !tc::mbar_wait(&ctl->acc_empty, (n - 1) & 1)) timed_out = true;
+            tc::tc_fence_after();
+          }
           if (r == 3) { TC_STAMP(1, n, 3) }
           const uint32_t d_tmem = tmem_base + (((5u * n + r) & 7u) << 6);
           // passes, smallest magnitude first: lo x Bhi, hi x Blo, hi x Bhi; descriptor offsets in
@@ -316,9 +314,14 @@ __global__ void __launch_bounds__(kTcThreads, 1)
                 tc::umma_f16<true>(d_tmem, a_r + a_t + 2u * ks, a_hi, b_r + b_t + 2u * ks, b_hi, idesc);
             }
           }
-          tc::umma_commit(&ctl->a_empty[r]);  // residue r's streams may be refilled
-          if (r == 2) nxt_active = tile_active(nx, len_n);
+          // commits only at the two hand-over points: a commit between residues drains the tensor
+          // pipe (measured: ~300 cycles per commit)
+          if (r == 2) {
+            tc::umma_commit(&ctl->a_empty[0]);  // the streams of residues 0-2 may be refilled
+            nxt_active = tile_active(nx, len_n);
+          }
         }
+        tc::umma_commit(&ctl->a_empty[1]);
         tc::umma_commit(&ctl->acc_full);
         TC_STAMP(1, n, 4)
         cur_active = nxt_active;
@@ -327,14 +330,15 @@ __global__ void __launch_bounds__(kTcThreads, 1)
     }
     __syncwarp();
   } else {
-    // ======================= EPILOGUE (warps 0-7) ===============================================
-    // thread = frame row = TMEM lane.  Two groups share every tile: group A (warps 0-3) reduces
-    // accumulator columns 0-31 of each residue (k1 = 0, 32, 1..15), group B (warps 4-7) columns
+    // ======================= EPILOGUE (warps 8-15) ==============================================
+    // thread = frame row = TMEM lane.  Two groups share every tile: group A (warps 8-11) reduces
+    // accumulator columns 0-31 of each residue (k1 = 0, 32, 1..15), group B (warps 12-15) columns
     // 32-63 (k1 = 16..31); warps w and w + 4 work on the same 32 rows.  Each mel bin is finished by
     // the group that feeds it; the 13 bins fed by both are parked by A in the staged row and
     // finished by B after the pair barrier.  B then stores the 32 rows with one TMA tensor store.
     tc::setmaxnreg_inc<kTcRegsEpilogue>();
-    const int group = warp >> 2, wq = warp & 3;
+    const int group = (warp - 8) >> 2, wq = warp & 3;
+    const int etid = tid - 256;
     const int row = wq * 32 + lane;
     uint32_t n = 0;
     const float eps = p.epsilon, log_eps = tp.log_eps;
@@ -357,7 +361,7 @@ __global__ void __launch_bounds__(kTcThreads, 1)
       const int t_first = j * tp.tout;  // first OUTPUT frame of this tile; row i holds frame t_first - halo + i
       const bool active = t_first < n_fr;
       const int t_row = t_first - tp.halo + row;
-      if (tid == 0 && j == 0 && p.n_frames) p.n_frames[b] = n_fr;
+      if (etid == 0 && j == 0 && p.n_frames) p.n_frames[b] = n_fr;
       // C == 1: the staged rows are free once the pair's previous TMA store has read them.  B waits
       // for that read and tells A, which only needs it before its first write to the rows.
       bool need_free = false;
@@ -378,20 +382,33 @@ __global__ void __launch_bounds__(kTcThreads, 1)
         if (lane == 0 && wq == 0) { TC_STAMP(2 + group, n, 1) }
         TC_DECL_ACC
         float P[20], Q[6], d[5][8];
+#if defined(TC_ABLATE_ELOAD)
+#pragma unroll
+        for (int r = 1; r < 5; ++r)
+#pragma unroll
+          for (int k = 0; k < 8; ++k) d[r][k] = __int_as_float(0x3f800000 + r * 977 + k * 131 + lane);
+#endif
         const uint32_t t_tile = tmem_base + lane_base;
         // one rolled loop per group over its 4 chunks of 8 accumulator columns (4 values of k1) per
         // residue; only the mel FFMAs (immediates, named accumulators) are per-chunk code
+#if defined(TC_ABLATE_EMATH)
+#define TC_RADIX_STEP(S)                                                                          \
+  { _Pragma("unroll") for (int k2 = 0; k2 < 5; ++k2) P[5 * (S) + k2] = d[k2][2 * (S)] + d[k2][2 * (S) + 1]; }
+#else
 #define TC_RADIX_STEP(S)                                                                          \
   {                                                                                               \
-    float xr[5], xi[5];                                                                           \
-    _Pragma("unroll") for (int r = 0; r < 5; ++r) {                                               \
-      xr[r] = d[r][2 * (S)];                                                                      \
-      xi[r] = d[r][2 * (S) + 1];                                                                  \
-    }                                                                                             \
-    tc_radix5_power(xr, xi, P[5 * (S)], P[5 * (S) + 1], P[5 * (S) + 2], P[5 * (S) + 3], P[5 * (S) + 4]); \
+    tc_f2 xc[5];                                                                                  \
+    _Pragma("unroll") for (int r = 0; r < 5; ++r) xc[r] = tc_pk(d[r][2 * (S)], d[r][2 * (S) + 1]); \
+    tc_radix5_power2(xc, P[5 * (S)], P[5 * (S) + 1], P[5 * (S) + 2], P[5 * (S) + 3], P[5 * (S) + 4]); \
   }
+#endif
+#if defined(TC_ABLATE_ELOAD)
+#define TC_LOAD_ROWS 1 /* (experiment: one TMEM load per chunk instead of five) */
+#else
+#define TC_LOAD_ROWS 5
+#endif
 #define TC_LOAD_CHUNK(CH)                                                                         \
-  _Pragma("unroll") for (int r = 0; r < 5; ++r) tc::tmem_ld8(t_tile + (((5u * n + r) & 7u) << 6) + 8 * (CH), d[r]); \
+  _Pragma("unroll") for (int r = 0; r < TC_LOAD_ROWS; ++r) tc::tmem_ld8(t_tile + (((5u * n + r) & 7u) << 6) + 8 * (CH), d[r]); \
   tc::tmem_ld_wait();                                                                             \
   if (((CH) & 3) == 3) {                                                                          \
     /* this thread's TMEM reads of the tile are done: hand the slots back before the arithmetic */ \
@@ -483,7 +500,7 @@ __global__ void __launch_bounds__(kTcThreads, 1)
         tc::named_bar_sync(9, 256);  // staged (and masked) rows visible to the 8 epilogue warps
         // ---- copy-out with delta / delta-delta: staged tile -> HBM, 128-bit, fully coalesced -----
         float* out_b = p.out + static_cast<int64_t>(b) * p.t_max * 240;
-        int i = tid / 20, quad = tid - 20 * i;
+        int i = etid / 20, quad = etid - 20 * i;
         for (int it = 0; it < 10; ++it) {
           const int t = t_first - tp.halo + i;
           if (i >= tp.halo && t < p.t_max) {

@@ -26,24 +26,21 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
       : "memory");
   return ok != 0;
 }
-// Bounded wait: a protocol bug must never hang the GPU.  Returns false on timeout.
-// (try_wait may suspend the thread for a while inside one poll, so bound by time, not by polls)
+// Bounded wait: a protocol bug must never hang the GPU.  Returns false on timeout (~0.1-1 s).
+// The poll loop is kept to three instructions (try_wait, counter, branch): waiting warps share the
+// issue slots of their SM sub-partition with the working ones.
+#ifndef TC_POLL_SLEEP_NS
+#define TC_POLL_SLEEP_NS 0
+#endif
 __device__ __forceinline__ bool mbar_wait(uint64_t* bar, uint32_t parity) {
-  const long long t0 = clock64();
-  while (!mbar_try_wait(bar, parity))
-    if (clock64() - t0 > 200000000LL) return false;  // ~0.1 s
-  return true;
-}
-// Same for a role with slack (the producers): sleep between polls, so that waiting warps do not burn
-// the issue slots the epilogue warps of the same SM sub-partition need.
-__device__ __forceinline__ bool mbar_wait_relaxed(uint64_t* bar, uint32_t parity) {
-  const long long t0 = clock64();
-  while (!mbar_try_wait(bar, parity)) {
-    __nanosleep(200);
-    if (clock64() - t0 > 200000000LL) return false;
+#pragma unroll 1
+  for (uint32_t i = 0; i < (1u << 22); ++i) {
+    if (mbar_try_wait(bar, parity)) return true;
+    if (TC_POLL_SLEEP_NS > 0) __nanosleep(TC_POLL_SLEEP_NS);
   }
-  return true;
+  return false;
 }
+__device__ __forceinline__ bool mbar_wait_relaxed(uint64_t* bar, uint32_t parity) { return mbar_wait(bar, parity); }
 
 // Shared-memory matrix descriptor (tcgen05 "smem descriptor"): start address, leading / stride byte
 // offsets (all >> 4), version 1, swizzle mode in bits [61,64).
