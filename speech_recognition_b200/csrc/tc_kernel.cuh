@@ -20,10 +20,11 @@
 //   * the radix-5 stage over r, power, sparse mel (FFMA immediates), log and the SpecAugment /
 //     delta / padding epilogue run on the CUDA cores, one thread per frame, straight from TMEM.
 //
-// Roles (288 threads, one persistent CTA per SM): warps 0-3 epilogue (thread = frame = TMEM lane),
-// warps 4-7 producers (PCM -> f16 hi/lo streams), warp 8 MMA issuer.  TMEM is used as a ring of
-// eight 64-column accumulator slots (a tile needs five), shared memory holds B (80 KB), one A stage
-// (85 KB) and the output staging tile (42 KB).
+// Roles (512 threads, one persistent CTA per SM, tiles of 128 frames): warp 0 MMA issuer, warps 1-7
+// producers (PCM -> exact f16 hi/lo streams), warps 8-15 two epilogue groups (thread = frame = TMEM
+// lane, each group reduces half of the accumulator columns).  TMEM is used as a ring of eight
+// 64-column accumulator slots (a tile needs five); shared memory holds B (80 KB), one A stage (85 KB)
+// and the output staging tile (42 KB).  DESIGN.md section 4.1 has the pipeline and the measurements.
 #pragma once
 
 #include <cuda.h>
