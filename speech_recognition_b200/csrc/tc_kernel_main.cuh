@@ -362,19 +362,22 @@ __global__ void __launch_bounds__(kTcThreads, 1)
       const bool active = t_first < n_fr;
       const int t_row = t_first - tp.halo + row;
       if (etid == 0 && j == 0 && p.n_frames) p.n_frames[b] = n_fr;
-      // C == 1: the staged rows are free once the pair's previous TMA store has read them.  B waits
-      // for that read and tells A, which only needs it before its first write to the rows.
-      bool need_free = false;
-      if (C == 1 && pending) {
-        if (group == 1) {
-          if (issuer) tc::bulk_wait_read();
-          __syncwarp();
-          tc::named_bar_arrive(bar_free, 64);
-        } else {
-          need_free = true;
-        }
-        pending = false;
-      }
+      // C == 1: the staged rows are free once the pair's previous TMA store has read them.  Nobody
+      // writes them before the group's last chunk (all finishing work is emitted there), so the
+      // hand-shake - B waits for that read and tells A - happens there, long after the read is done.
+      bool need_free = C == 1 && pending;
+      pending = false;
+#define TC_ROWS_FREE()                                                                            \
+  if (need_free) {                                                                                \
+    if (group == 1) {                                                                             \
+      if (issuer) tc::bulk_wait_read(); /* async-groups belong to the thread that committed them */ \
+      __syncwarp();                                                                               \
+      tc::named_bar_arrive(bar_free, 64);                                                         \
+    } else {                                                                                      \
+      tc::named_bar_sync(bar_free, 64);                                                           \
+    }                                                                                             \
+    need_free = false;                                                                            \
+  }
       if (active) {
         if (lane == 0 && wq == 0) { TC_STAMP(2 + group, n, 0) }
         if (!timed_out && !tc::mbar_wait(&ctl->acc_full, n & 1)) timed_out = true;
@@ -416,88 +419,6 @@ __global__ void __launch_bounds__(kTcThreads, 1)
     tc::mbar_arrive(&ctl->acc_empty);                                                             \
     if (lane == 0 && wq == 0) { TC_STAMP(2 + group, n, 2) }                                       \
   }
-#if defined(TC_EPI_SPLIT)
-        // one loop per group (fewer live accumulators), two TMEM register buffers: the loads of chunk
-        // c + 1 are in flight while chunk c is computed, and TMEM is released one chunk earlier
-        float dB[5][8];
-#define TC_LOADX(D, CH)                                                                           \
-  _Pragma("unroll") for (int r = 0; r < 5; ++r) tc::tmem_ld8(t_tile + (((5u * n + r) & 7u) << 6) + 8 * (CH), D[r]);
-#define TC_RELEASE()                                                                              \
-  tc::tc_fence_before();                                                                          \
-  tc::mbar_arrive(&ctl->acc_empty);                                                               \
-  if (lane == 0 && wq == 0) { TC_STAMP(2 + group, n, 2) }
-#define TC_STEPX(D, S)                                                                            \
-  {                                                                                               \
-    tc_f2 xc[5];                                                                                  \
-    _Pragma("unroll") for (int r = 0; r < 5; ++r) xc[r] = tc_pk(D[r][2 * (S)], D[r][2 * (S) + 1]); \
-    tc_radix5_power2(xc, P[5 * (S)], P[5 * (S) + 1], P[5 * (S) + 2], P[5 * (S) + 3], P[5 * (S) + 4]); \
-  }
-        if (group == 0) {
-          TC_LOADX(d, 0)
-#pragma unroll 1
-          for (int c = 0; c < 4; c += 2) {
-            tc::tmem_ld_wait();
-            TC_LOADX(dB, c + 1)
-            if (c == 0) {
-              // columns 0 / 1 hold the real k1 = 0 and k1 = 32 terms: Y_r[32] = R_r * e^{-i pi r / 5}
-              float x[5];
-#pragma unroll
-              for (int r = 0; r < 5; ++r) x[r] = d[r][0];
-              tc_radix5_power_real(x, Q[0], Q[1], Q[2]);
-              const float cr[5] = {1.0f, 0.80901699437494742410f, 0.30901699437494742410f, -0.30901699437494742410f,
-                                   -0.80901699437494742410f};
-              const float sr[5] = {0.0f, 0.58778525229247312917f, 0.95105651629515357212f, 0.95105651629515357212f,
-                                   0.58778525229247312917f};
-              float xr[5], xi[5], p3, p4;
-#pragma unroll
-              for (int r = 0; r < 5; ++r) {
-                xr[r] = d[r][1] * cr[r];
-                xi[r] = -d[r][1] * sr[r];
-              }
-              tc_radix5_power(xr, xi, Q[3], Q[4], Q[5], p3, p4);
-            } else {
-              TC_STEPX(d, 0)
-            }
-            TC_STEPX(d, 1)
-            TC_STEPX(d, 2)
-            TC_STEPX(d, 3)
-            if (need_free) {
-              tc::named_bar_sync(bar_free, 64);
-              need_free = false;
-            }
-            if (c == 0) { TC_MEL_CHUNK_0(Q, P); } else { TC_MEL_CHUNK_2(Q, P); }
-            tc::tmem_ld_wait();
-            if (c == 0) { TC_LOADX(d, 2) } else { TC_RELEASE() }
-            TC_STEPX(dB, 0)
-            TC_STEPX(dB, 1)
-            TC_STEPX(dB, 2)
-            TC_STEPX(dB, 3)
-            if (c == 0) { TC_MEL_CHUNK_1(Q, P); } else { TC_MEL_CHUNK_3(Q, P); }
-          }
-        } else {
-          TC_LOADX(d, 4)
-#pragma unroll 1
-          for (int c = 4; c < 8; c += 2) {
-            tc::tmem_ld_wait();
-            TC_LOADX(dB, c + 1)
-            TC_STEPX(d, 0)
-            TC_STEPX(d, 1)
-            TC_STEPX(d, 2)
-            TC_STEPX(d, 3)
-            if (c == 4) { TC_MEL_CHUNK_4(Q, P); } else { TC_MEL_CHUNK_6(Q, P); }
-            tc::tmem_ld_wait();
-            if (c == 4) { TC_LOADX(d, 6) } else { TC_RELEASE() }
-            TC_STEPX(dB, 0)
-            TC_STEPX(dB, 1)
-            TC_STEPX(dB, 2)
-            TC_STEPX(dB, 3)
-            if (c == 4) { TC_MEL_CHUNK_5(Q, P); } else { TC_MEL_CHUNK_7(Q, P); }
-          }
-        }
-#undef TC_LOADX
-#undef TC_RELEASE
-#undef TC_STEPX
-#else
         // both groups run the SAME loop code (instruction-cache footprint): group A chunks 0-3, B 4-7
         const int c0 = 4 * group;
 #pragma unroll 1
@@ -526,10 +447,9 @@ __global__ void __launch_bounds__(kTcThreads, 1)
           TC_RADIX_STEP(1)
           TC_RADIX_STEP(2)
           TC_RADIX_STEP(3)
-          if (need_free) {
-            tc::named_bar_sync(bar_free, 64);
-            need_free = false;
-          }
+          // B announces early (its first chunk: the read has long finished), A checks late (its last
+          // chunk, the first one that writes rows): neither waits for the other in practice
+          if (c == c0 + 3 - 3 * group) { TC_ROWS_FREE() }
           switch (c) {
             case 0: TC_MEL_CHUNK_0(Q, P); break;
             case 1: TC_MEL_CHUNK_1(Q, P); break;
@@ -541,7 +461,6 @@ __global__ void __launch_bounds__(kTcThreads, 1)
             default: TC_MEL_CHUNK_7(Q, P); break;
           }
         }
-#endif
         if (lane == 0 && wq == 0) { TC_STAMP(2 + group, n, 3) }
         if (group == 1) {
           // A's finished bins and parked partial sums of this row are in shared memory
@@ -557,7 +476,8 @@ __global__ void __launch_bounds__(kTcThreads, 1)
         if (lane == 0 && wq == 0) { TC_STAMP(2 + group, n, 5) }
         ++n;
       }
-      if (need_free) tc::named_bar_sync(bar_free, 64);  // (tile of padding only: keep the barrier phases paired)
+      TC_ROWS_FREE()  // (tile of padding only: keep the barrier phases paired, B zero-fills below)
+#undef TC_ROWS_FREE
 
       if (C == 1) {
         // ---- group B stores the pair's 32 staged rows with ONE TMA tensor store: the box is
