@@ -178,6 +178,20 @@ int b200mel_create(const b200mel_config* config, int device, b200mel_handle** ou
 #ifdef B200MEL_WITH_TC
   h->tc_ok = tc_plan_build(p, h->tc, h->max_smem_optin);
   if (h->tc_ok) {
+    // the epilogue's fast log must reproduce logf(epsilon) exactly for silence (see tc_finish)
+    float* d_probe = nullptr;
+    float probe = 0.0f;
+    if (cudaMalloc(reinterpret_cast<void**>(&d_probe), sizeof(float)) == cudaSuccess) {
+      tc_eps_probe_kernel<<<1, 1>>>(p.cfg.epsilon, d_probe);
+      if (cudaMemcpy(&probe, d_probe, sizeof(float), cudaMemcpyDeviceToHost) != cudaSuccess) h->tc_ok = false;
+      cudaFree(d_probe);
+    } else {
+      h->tc_ok = false;
+    }
+    cudaGetLastError();
+    if (std::memcmp(&probe, &h->tc.log_eps, sizeof(float)) != 0) h->tc_ok = false;
+  }
+  if (h->tc_ok) {
     // per-device function attribute: set it while this handle's device is current
     if (cudaFuncSetAttribute(tc_frontend_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmemTotal) != cudaSuccess ||
         cudaFuncSetAttribute(tc_frontend_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmemTotal) != cudaSuccess) {

@@ -12,13 +12,18 @@ struct TcCtl {
   uint32_t tmem_base;
 };
 
-// log(mel + eps); exactly log(eps) for silence (the reference's golden fixture pins that value)
-__device__ __forceinline__ float tc_finish(float acc, float eps, float log_eps) {
-  // mel + eps >= 1e-12 is a normal float: one MUFU.LG2 + one FMUL (abs error ~ 2^-22 * |log|)
+// log(mel + eps): one MUFU.LG2 + one FMUL (abs error ~ 2^-22 * |log|; mel + eps >= eps is a normal
+// float).  Silence must give exactly logf(eps) - the reference's golden fixture pins that value - and
+// it does: acc = 0 makes the argument eps itself, and tc_eps_probe_kernel checks at handle creation
+// that this expression reproduces logf(eps) bit-for-bit (true for the reference's 1e-12); a handle
+// whose epsilon fails the probe does not get the tensor-core kernel.
+__device__ __forceinline__ float tc_log_fast(float v) {
   float l2;
-  asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(l2) : "f"(acc + eps));
-  return acc == 0.0f ? log_eps : l2 * 0.69314718055994530942f;
+  asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(l2) : "f"(v));
+  return l2 * 0.69314718055994530942f;
 }
+__device__ __forceinline__ float tc_finish(float acc, float eps, float) { return tc_log_fast(acc + eps); }
+__global__ void tc_eps_probe_kernel(float eps, float* out) { out[0] = tc_log_fast(0.0f + eps); }
 
 #if defined(TC_ABLATE_ESTS)
 #define TC_ROW_ST(PTR, V) if (eps == 12345.0f) *(PTR) = (V) /* (experiment: no staging stores) */
