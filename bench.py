@@ -125,6 +125,13 @@ def cpu_reference_run(n_utt, steps, warmup, threads=0):
     cannot be installed here) on `n_utt` utterances of the same workload per step."""
     from oracle.ref_c import RefPlan
 
+    if threads <= 0:
+        # every host core this process may use - explicitly, because torchrun exports
+        # OMP_NUM_THREADS=1 and the OpenMP default would then time a single thread
+        try:
+            threads = len(os.sched_getaffinity(0))
+        except AttributeError:
+            threads = os.cpu_count() or 1
     plan = RefPlan("log-mel-spectrogram", **CFG)
     pcm = synth_batch(1234, n_utt)
     out = np.empty((n_utt, T, 80, 1), np.float32)
