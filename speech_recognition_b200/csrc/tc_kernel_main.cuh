@@ -8,7 +8,8 @@ struct TcCtl {
   uint64_t a_full[2];   // producers (224 arrivals) -> MMA: the phase's streams (hi, lo) are in smem
   uint64_t a_empty[2];  // tcgen05.commit -> producers: the MMAs that read the phase's streams are done
   uint64_t acc_full;    // tcgen05.commit -> epilogue: the 5 accumulators of this tile are complete
-  uint64_t acc_empty;   // epilogue (128 arrivals) -> MMA: this tile's TMEM slots may be overwritten
+  uint64_t acc_empty;   // epilogue (256 arrivals) -> MMA: this tile's TMEM slots may be overwritten
+  uint64_t b_full;      // TMA bulk copy -> MMA: the B operand image has landed in shared memory
   uint32_t tmem_base;
 };
 
@@ -101,12 +102,8 @@ __global__ void __launch_bounds__(kTcThreads, 1)
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
 
   // ---- one-time setup ------------------------------------------------------------------------
-  {
-    const uint4* src = reinterpret_cast<const uint4*>(tp.b_image);
-    uint4* dst = reinterpret_cast<uint4*>(sB);
-    for (int i = tid; i < 10 * kTcBBytes / 16; i += kTcThreads) dst[i] = __ldg(src + i);
-  }
   if (tid == 0) {
+    tc::mbar_init(&ctl->b_full, 1);
     for (int r = 0; r < 2; ++r) {
       tc::mbar_init(&ctl->a_full[r], kTcProducerThreads);
       tc::mbar_init(&ctl->a_empty[r], 1);
@@ -114,8 +111,12 @@ __global__ void __launch_bounds__(kTcThreads, 1)
     tc::mbar_init(&ctl->acc_full, 1);
     tc::mbar_init(&ctl->acc_empty, 256);
     tc::fence_mbar_init();
+    // B operand (80 KB, constant): two bulk copies by the TMA engine, only the MMA issuer waits for
+    // them - producers and epilogue warps start on the first tile at once
+    tc::mbar_expect_tx(&ctl->b_full, 10 * kTcBBytes);
+    tc::bulk_copy_g2s(tc::smem_u32(sB), tp.b_image, 5 * kTcBBytes, &ctl->b_full);
+    tc::bulk_copy_g2s(tc::smem_u32(sB) + 5 * kTcBBytes, tp.b_image + 5 * kTcBBytes, 5 * kTcBBytes, &ctl->b_full);
   }
-  tc::fence_async_smem();
   __syncthreads();
   if (warp == kTcMmaWarp) tc::tmem_alloc(&ctl->tmem_base, 512);
   tc::tc_fence_before();
@@ -272,6 +273,7 @@ __global__ void __launch_bounds__(kTcThreads, 1)
       const uint64_t b_base = tc::make_smem_desc(tc::smem_u32(sB), 16, 1024, tc::kLayoutSw128);
       const uint32_t a_lo0 = static_cast<uint32_t>(a_base), a_hi = static_cast<uint32_t>(a_base >> 32);
       const uint32_t b_lo0 = static_cast<uint32_t>(b_base), b_hi = static_cast<uint32_t>(b_base >> 32);
+      if (!tc::mbar_wait(&ctl->b_full, 0)) timed_out = true;
       // "is this tile active" is evaluated one tile ahead, while the tensor pipe is busy with queued
       // MMAs, so that the issuing thread has nothing to do between two tiles
       auto tile_len = [&](int t) -> int32_t { return t < tp.total_tiles ? __ldg(p.lengths + t / tp.tiles_per_utt) : 0; };

@@ -125,6 +125,16 @@ __device__ __forceinline__ void tma_store_3d(const void* tmap, uint32_t ssrc, in
                "r"(c1), "r"(c2), "r"(ssrc)
                : "memory");
 }
+// Bulk asynchronous copy global -> shared (TMA engine), completion counted in bytes on an mbarrier.
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.expect_tx.shared::cta.b64 st, [%0], %1;\n\t}" ::"r"(smem_u32(bar)), "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void bulk_copy_g2s(uint32_t sdst, const void* gsrc, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(sdst), "l"(gsrc),
+               "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
 // Asynchronous prefetch of a global range into L2 (addr 16-byte aligned, size a multiple of 16).
 __device__ __forceinline__ void prefetch_l2(const void* gsrc, uint32_t bytes) {
   asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(gsrc), "r"(bytes) : "memory");
