@@ -124,6 +124,11 @@ __global__ void __launch_bounds__(kTcThreads, 1)
   tc::tc_fence_after();
   const uint32_t tmem_base = ctl->tmem_base;
   bool timed_out = false;
+  // Programmatic dependent launch: everything above (barriers, TMEM, the constant B image) may overlap
+  // the tail of the previous kernel in the stream; caller data (PCM, lengths, tables, the output) is
+  // only touched after that kernel has completed.
+  tc::pdl_launch_dependents();
+  tc::pdl_wait();
 
   if (warp >= 1 && warp < 8) {
     // ======================= PRODUCERS (warps 1-7: 224 threads) =================================
@@ -578,8 +583,19 @@ inline int tc_launch(const TcPlan& tc, const KernelParams& kp, int sm_count, cud
   const int grid = total < sm_count ? static_cast<int>(total) : sm_count;
   alignas(64) CUtensorMap map;
   std::memset(&map, 0, sizeof(map));
+  cudaLaunchConfig_t lc;
+  std::memset(&lc, 0, sizeof(lc));
+  lc.gridDim = dim3(grid);
+  lc.blockDim = dim3(kTcThreads);
+  lc.dynamicSmemBytes = kTcSmemTotal;
+  lc.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  lc.attrs = attr;
+  lc.numAttrs = 1;
   if (kp.C == 3) {
-    tc_frontend_kernel<3><<<grid, kTcThreads, kTcSmemTotal, st>>>(kp, tp, map);
+    if (cudaLaunchKernelEx(&lc, tc_frontend_kernel<3>, kp, tp, map) != cudaSuccess) return 1;
   } else {
     // output viewed as a 3-D tensor [B][t_max][80] f32; box = [1][32][84]
     TcEncodeTiledFn enc = tc_encode_fn();
@@ -591,7 +607,7 @@ inline int tc_launch(const TcPlan& tc, const KernelParams& kp, int sm_count, cud
     if (enc(&map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, kp.out, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
             CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
       return 2;
-    tc_frontend_kernel<1><<<grid, kTcThreads, kTcSmemTotal, st>>>(kp, tp, map);
+    if (cudaLaunchKernelEx(&lc, tc_frontend_kernel<1>, kp, tp, map) != cudaSuccess) return 1;
   }
   return cudaGetLastError() == cudaSuccess ? 0 : 1;
 }

@@ -135,6 +135,10 @@ __device__ __forceinline__ void bulk_copy_g2s(uint32_t sdst, const void* gsrc, u
                "r"(bytes), "r"(smem_u32(bar))
                : "memory");
 }
+// Programmatic dependent launch: let the next kernel of the stream be scheduled early / wait for the
+// previous kernel's completion and memory before touching anything it may have written or read.
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 // Asynchronous prefetch of a global range into L2 (addr 16-byte aligned, size a multiple of 16).
 __device__ __forceinline__ void prefetch_l2(const void* gsrc, uint32_t bytes) {
   asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(gsrc), "r"(bytes) : "memory");
