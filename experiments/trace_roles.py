@@ -18,9 +18,11 @@ assert lib.b200mel_debug_trace(buf) == 0
 t = np.array(buf[:]).reshape(4, 32, 8)
 t0 = t[t > 0].min()
 names = ["P ", "M ", "EA", "EB"]
-ev = {0: ["start", "w0", "w1", "w2", "w3", "w4", "done"], 1: ["top", "afull0", "pre_accE", "accE_ok", "committed"],
+ev = {0: ["start", "w0", "w1", "w2", "w3", "arr_w4", "done", "arr_w7"], 1: ["top", "afull0", "pre_accE", "accE_ok", "committed", "afull1_ok"],
       2: ["top", "accfull", "released", "loopend", "", "done"], 3: ["top", "accfull", "released", "loopend", "ready", "done"]}
-for n in range(6, 12):
+print("kernel: top=%d setup_done=%d dep_wait_done=%d teardown=%d" % tuple(t[1, 31, e] - t0 for e in range(4)))
+t[1, 31, :] = 0
+for n in list(range(0, 2)) + list(range(9, 12)) + list(range(20, 21)):
     print("tile", n)
     for r in range(4):
         print("  ", names[r], " ".join("%s=%d" % (ev[r][e], t[r, n, e] - t0) for e in range(len(ev[r])) if ev[r][e] and t[r, n, e] > 0))

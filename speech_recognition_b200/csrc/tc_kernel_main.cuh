@@ -88,6 +88,23 @@ __device__ long long g_tc_trace[4][32][8];
 #define TC_STAMP(ROLE, N, EV)
 #endif
 
+// (utterance, tile within the utterance) of a tile index, advanced by the grid stride without a division
+struct TcTileIter {
+  int b, j;
+  __device__ __forceinline__ void init(int t, int tiles_per_utt) {
+    b = t / tiles_per_utt;
+    j = t - b * tiles_per_utt;
+  }
+  __device__ __forceinline__ void step(int step_b, int step_j, int tiles_per_utt) {
+    b += step_b;
+    j += step_j;
+    if (j >= tiles_per_utt) {
+      j -= tiles_per_utt;
+      ++b;
+    }
+  }
+};
+
 template <int C>
 __global__ void __launch_bounds__(kTcThreads, 1)
     tc_frontend_kernel(const KernelParams p, const TcParams tp, const __grid_constant__ CUtensorMap out_map) {
@@ -102,7 +119,8 @@ __global__ void __launch_bounds__(kTcThreads, 1)
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
 
   // ---- one-time setup ------------------------------------------------------------------------
-  if (tid == 0) {
+  if (tid == 0) { TC_STAMP(1, 31, 0) }
+  if (tid == 32) {
     tc::mbar_init(&ctl->b_full, 1);
     for (int r = 0; r < 2; ++r) {
       tc::mbar_init(&ctl->a_full[r], kTcProducerThreads);
@@ -117,8 +135,22 @@ __global__ void __launch_bounds__(kTcThreads, 1)
     tc::bulk_copy_g2s(tc::smem_u32(sB), tp.b_image, 5 * kTcBBytes, &ctl->b_full);
     tc::bulk_copy_g2s(tc::smem_u32(sB) + 5 * kTcBBytes, tp.b_image + 5 * kTcBBytes, 5 * kTcBBytes, &ctl->b_full);
   }
-  __syncthreads();
   if (warp == kTcMmaWarp) tc::tmem_alloc(&ctl->tmem_base, 512);
+  const int step_b = gridDim.x / tp.tiles_per_utt, step_j = gridDim.x - step_b * tp.tiles_per_utt;
+  if (tid == 64 && p.offsets == nullptr && (reinterpret_cast<uintptr_t>(p.pcm) & 15) == 0 && (p.row_stride & 7) == 0) {
+    // Pull the PCM range of this CTA's first tile into L2 before anything else: its loads otherwise
+    // start only after the (cold) length fetch.  The range is bounded by the row, not by the utterance
+    // length (not known yet); an L2 prefetch has no architectural effect, so it may precede the
+    // dependency wait below.
+    TcTileIter it;
+    it.init(blockIdx.x, tp.tiles_per_utt);
+    int64_t s0 = 160 * static_cast<int64_t>(it.j * tp.tout - tp.halo), s1 = s0 + 129 * 160;
+    if (s0 < 0) s0 = 0;
+    if (s1 > p.row_stride) s1 = p.row_stride;
+    if (s1 > s0)
+      tc::prefetch_l2(static_cast<const int16_t*>(p.pcm) + static_cast<int64_t>(it.b) * p.row_stride + s0,
+                      static_cast<uint32_t>(2 * (s1 - s0)));
+  }
   tc::tc_fence_before();
   __syncthreads();
   tc::tc_fence_after();
@@ -128,7 +160,9 @@ __global__ void __launch_bounds__(kTcThreads, 1)
   // the tail of the previous kernel in the stream; caller data (PCM, lengths, tables, the output) is
   // only touched after that kernel has completed.
   tc::pdl_launch_dependents();
+  if (tid == 0) { TC_STAMP(1, 31, 1) }
   tc::pdl_wait();
+  if (tid == 0) { TC_STAMP(1, 31, 2) }
 
   if (warp >= 1 && warp < 8) {
     // ======================= PRODUCERS (warps 1-7: 224 threads) =================================
@@ -148,15 +182,20 @@ __global__ void __launch_bounds__(kTcThreads, 1)
     // (length, offset) of the utterances of this CTA's next two tiles, fetched ahead of use.  Offsets
     // are kept in 8-sample blocks (bit 31 = "not 16-byte aligned": such utterances take the slow path).
     const bool pcm_al = (reinterpret_cast<uintptr_t>(p.pcm) & 15) == 0;
-    auto fetch_len = [&](int t) -> int32_t { return t < tp.total_tiles ? __ldg(p.lengths + t / tp.tiles_per_utt) : 0; };
-    auto fetch_blk = [&](int t) -> uint32_t {
+    auto fetch_len = [&](int t, int bt) -> int32_t { return t < tp.total_tiles ? __ldg(p.lengths + bt) : 0; };
+    auto fetch_blk = [&](int t, int bt) -> uint32_t {
       if (t >= tp.total_tiles) return 0x80000000u;
-      const int bt = t / tp.tiles_per_utt;
       const int64_t o = p.offsets ? __ldg(p.offsets + bt) : static_cast<int64_t>(bt) * p.row_stride;
       return (pcm_al && (o & 7) == 0) ? static_cast<uint32_t>(o >> 3) : 0x80000000u;
     };
-    int32_t len1 = fetch_len(blockIdx.x), len2 = fetch_len(blockIdx.x + gridDim.x);
-    uint32_t bb1 = fetch_blk(blockIdx.x), bb2 = fetch_blk(blockIdx.x + gridDim.x);
+    TcTileIter it0, it1, it2;  // this tile, the CTA's next one, the one after
+    it0.init(blockIdx.x, tp.tiles_per_utt);
+    it1 = it0;
+    it1.step(step_b, step_j, tp.tiles_per_utt);
+    it2 = it1;
+    it2.step(step_b, step_j, tp.tiles_per_utt);
+    int32_t len1 = fetch_len(blockIdx.x, it0.b), len2 = fetch_len(blockIdx.x + gridDim.x, it1.b);
+    uint32_t bb1 = fetch_blk(blockIdx.x, it0.b), bb2 = fetch_blk(blockIdx.x + gridDim.x, it1.b);
     const uint4* pcm16 = reinterpret_cast<const uint4*>(p.pcm);
     uint32_t w[3][20];  // this thread's groups: raw words (two samples each), XOR-ed in place before use
     bool preloaded = false;
@@ -171,16 +210,18 @@ __global__ void __launch_bounds__(kTcThreads, 1)
     w[I][4 * q + 3] = v.w;                                                                             \
   }
     for (int tile = blockIdx.x; tile < tp.total_tiles; tile += gridDim.x) {
-      const int b = tile / tp.tiles_per_utt, j = tile - b * tp.tiles_per_utt;
+      const int b = it0.b, j = it0.j, jn = it1.j;
       const int32_t len = len1;
       const uint32_t bb = bb1;
       const int nx = tile + gridDim.x;  // next tile of this CTA: (len1, bb1) after the shift
       len1 = len2;
       bb1 = bb2;
-      len2 = fetch_len(nx + gridDim.x);
-      bb2 = fetch_blk(nx + gridDim.x);
+      len2 = fetch_len(nx + gridDim.x, it2.b);
+      bb2 = fetch_blk(nx + gridDim.x, it2.b);
+      it0 = it1;
+      it1 = it2;
+      it2.step(step_b, step_j, tp.tiles_per_utt);
       // next tile: first block, clamp range (all in absolute 8-sample blocks; requires < 2^31 blocks)
-      const int jn = nx - (nx / tp.tiles_per_utt) * tp.tiles_per_utt;
       const bool next_ok = !(bb1 & 0x80000000u) && jn * tp.tout < frames_of(len1, 320, 160);
       const int32_t nb_lo = static_cast<int32_t>(bb1), nb_hi = nb_lo + (len1 >> 3) - 1;
       const int32_t nb_0 = nb_lo + 20 * (jn * tp.tout - tp.halo);
@@ -244,6 +285,8 @@ __global__ void __launch_bounds__(kTcThreads, 1)
         }
         tc::fence_async_smem();
         tc::mbar_arrive(&ctl->a_full[1]);
+        if (ptid == 96) { TC_STAMP(0, n, 5) }
+        if (ptid == 192) { TC_STAMP(0, n, 7) }
         // the registers are free: start loading the next tile's PCM (its range is in L2 by now).
         // After the fence on purpose - the fence waits for this thread's outstanding loads.
         if (next_ok) {
@@ -281,19 +324,21 @@ __global__ void __launch_bounds__(kTcThreads, 1)
       if (!tc::mbar_wait(&ctl->b_full, 0)) timed_out = true;
       // "is this tile active" is evaluated one tile ahead, while the tensor pipe is busy with queued
       // MMAs, so that the issuing thread has nothing to do between two tiles
-      auto tile_len = [&](int t) -> int32_t { return t < tp.total_tiles ? __ldg(p.lengths + t / tp.tiles_per_utt) : 0; };
-      auto tile_active = [&](int t, int32_t len_t) -> bool {
-        const int jt = t - (t / tp.tiles_per_utt) * tp.tiles_per_utt;
+      auto tile_len = [&](int t, int bt) -> int32_t { return t < tp.total_tiles ? __ldg(p.lengths + bt) : 0; };
+      auto tile_active = [&](int t, int jt, int32_t len_t) -> bool {
         return t < tp.total_tiles && jt * tp.tout < frames_of(len_t, 320, 160);
       };
-      bool cur_active = tile_active(blockIdx.x, tile_len(blockIdx.x));
+      TcTileIter it;  // the CTA's NEXT tile inside the loop
+      it.init(blockIdx.x, tp.tiles_per_utt);
+      bool cur_active = tile_active(blockIdx.x, it.j, tile_len(blockIdx.x, it.b));
       for (int tile = blockIdx.x; tile < tp.total_tiles; tile += gridDim.x) {
         const int nx = tile + gridDim.x;
+        it.step(step_b, step_j, tp.tiles_per_utt);
         if (!cur_active) {
-          cur_active = tile_active(nx, tile_len(nx));
+          cur_active = tile_active(nx, it.j, tile_len(nx, it.b));
           continue;
         }
-        const int32_t len_n = tile_len(nx);  // consumed after the MMAs of residue 2 are queued
+        const int32_t len_n = tile_len(nx, it.b);  // consumed after the MMAs of residue 2 are queued
         bool nxt_active = false;
 #pragma unroll 1
         for (int r = 0; r < 5; ++r) {
@@ -307,6 +352,7 @@ __global__ void __launch_bounds__(kTcThreads, 1)
             TC_STAMP(1, n, 2)
             // slots of residues 3, 4 were residues 0, 1 of the previous tile: wait for its epilogue
             if (!timed_out && !tc::mbar_wait(&ctl->a_full[1], n & 1)) timed_out = true;
+            TC_STAMP(1, n, 5)
             if (n > 0 && !timed_out && !tc::mbar_wait(&ctl->acc_empty, (n - 1) & 1)) timed_out = true;
             tc::tc_fence_after();
           }
@@ -330,7 +376,7 @@ __global__ void __launch_bounds__(kTcThreads, 1)
           // pipe (measured: ~300 cycles per commit)
           if (r == 2) {
             tc::umma_commit(&ctl->a_empty[0]);  // the streams of residues 0-2 may be refilled
-            nxt_active = tile_active(nx, len_n);
+            nxt_active = tile_active(nx, it.j, len_n);
           }
         }
         tc::umma_commit(&ctl->a_empty[1]);
@@ -361,14 +407,14 @@ __global__ void __launch_bounds__(kTcThreads, 1)
     const uint32_t bar_ready = 1 + wq, bar_free = 5 + wq;  // pair barriers (64 threads)
     bool pending = false;  // C == 1: the pair's previous TMA store may still be reading the staged rows
     bool issuer = false;   // this thread issued it (bulk async-groups are per thread)
-    int32_t len_nxt = blockIdx.x < tp.total_tiles ? __ldg(p.lengths + blockIdx.x / tp.tiles_per_utt) : 0;
+    TcTileIter it;
+    it.init(blockIdx.x, tp.tiles_per_utt);
+    int32_t len_nxt = __ldg(p.lengths + it.b);
     for (int tile = blockIdx.x; tile < tp.total_tiles; tile += gridDim.x) {
-      const int b = tile / tp.tiles_per_utt, j = tile - b * tp.tiles_per_utt;
+      const int b = it.b, j = it.j;
       const int32_t len = len_nxt;  // fetched one tile ahead
-      {
-        const int nx = tile + gridDim.x;
-        if (nx < tp.total_tiles) len_nxt = __ldg(p.lengths + nx / tp.tiles_per_utt);
-      }
+      it.step(step_b, step_j, tp.tiles_per_utt);
+      if (tile + gridDim.x < tp.total_tiles) len_nxt = __ldg(p.lengths + it.b);
       const int n_fr = frames_of(len, 320, 160);
       const int t_first = j * tp.tout;  // first OUTPUT frame of this tile; row i holds frame t_first - halo + i
       const bool active = t_first < n_fr;
@@ -549,6 +595,7 @@ __global__ void __launch_bounds__(kTcThreads, 1)
   if (timed_out && p.status) atomicOr(p.status, 0x100);
   tc::tc_fence_before();
   __syncthreads();
+  if (tid == 0) { TC_STAMP(1, 31, 3) }
   if (warp == kTcMmaWarp) tc::tmem_dealloc(tmem_base, 512);
 }
 
