@@ -116,7 +116,9 @@ __global__ void __launch_bounds__(kTcThreads, 1)
   float* sOut = reinterpret_cast<float*>(smem + kTcSmemOut);
   TcCtl* ctl = reinterpret_cast<TcCtl*>(smem + kTcSmemCtl);
 
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  // warp index through a shuffle: the compiler then knows it is warp-uniform (uniform registers and
+  // branches for everything derived from it: roles, TMEM addresses, chunk dispatch)
+  const int tid = threadIdx.x, warp = __shfl_sync(0xffffffffu, tid >> 5, 0), lane = tid & 31;
 
   // ---- one-time setup ------------------------------------------------------------------------
   if (tid == 0) { TC_STAMP(1, 31, 0) }
