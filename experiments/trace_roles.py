@@ -6,7 +6,8 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from speech_recognition_b200 import FeatureFrontend, _lib
 cfg = dict(sample_rate=16000, frame_length=320, frame_step=160, fft_length=320, num_mel_bins=80,
            lower_edge_hertz=80.0, upper_edge_hertz=7600.0)
-fe = FeatureFrontend("log-mel-spectrogram", **cfg, device="cuda:0")
+SA = dict(enable=True, W=None, F=27, m_F=2, T=100, p=1.0, m_T=2) if os.environ.get("TRACE_SA") else None
+fe = FeatureFrontend("log-mel-spectrogram", **cfg, spec_augment=SA, device="cuda:0")
 x = torch.randint(-3000, 3000, (256, 240000), dtype=torch.int16, device="cuda")
 for _ in range(3):
     out, nf = fe(x, kernel="tc")
@@ -19,7 +20,7 @@ t = np.array(buf[:]).reshape(4, 32, 8)
 t0 = t[t > 0].min()
 names = ["P ", "M ", "EA", "EB"]
 ev = {0: ["start", "w0", "w1", "w2", "w3", "arr_w4", "done", "arr_w7"], 1: ["top", "afull0", "pre_accE", "accE_ok", "committed", "afull1_ok"],
-      2: ["top", "accfull", "released", "loopend", "", "done"], 3: ["top", "accfull", "released", "loopend", "ready", "done"]}
+      2: ["top", "accfull", "released", "loopend", "", "done", "m_start", "m_time"], 3: ["top", "accfull", "released", "loopend", "ready", "done", "m_built", "m_end"]}
 print("kernel: top=%d setup_done=%d dep_wait_done=%d teardown=%d" % tuple(t[1, 31, e] - t0 for e in range(4)))
 t[1, 31, :] = 0
 for n in list(range(0, 2)) + list(range(9, 12)) + list(range(20, 21)):

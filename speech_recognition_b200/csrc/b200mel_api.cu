@@ -347,10 +347,14 @@ int b200mel_forward(b200mel_handle* h, const void* pcm, int32_t pcm_dtype, const
   const bool tc_aligned = (reinterpret_cast<uintptr_t>(out) & 15) == 0;
   if (kernel == B200MEL_KERNEL_TC && !tc_aligned)
     return fail(B200MEL_ERR_INVALID_ARGUMENT, "the tensor-core kernel needs a 16-byte aligned output buffer");
-  if (h->tc_ok && kernel != B200MEL_KERNEL_GENERIC && t_max > 0 && pcm_dtype == B200MEL_PCM_I16 && tc_aligned) {
+  if (kernel == B200MEL_KERNEL_TC && kp.n_masks_f + kp.n_masks_t > 16)
+    return fail(B200MEL_ERR_INVALID_ARGUMENT, "the tensor-core kernel handles at most 16 SpecAugment masks per utterance");
+  // (the tensor-core kernel keeps one mask-table entry per lane: at most 16 masks per utterance)
+  if (h->tc_ok && kernel != B200MEL_KERNEL_GENERIC && t_max > 0 && pcm_dtype == B200MEL_PCM_I16 && tc_aligned &&
+      kp.n_masks_f + kp.n_masks_t <= 16) {
     const int n_masks = kp.n_masks_f + kp.n_masks_t;
     int32_t* tmp_table = nullptr;
-    if (n_masks > 0 && !mask_table) {
+    if (n_masks > 0 && !mask_table && !tc_draws_in_kernel(kp, h->sm_count)) {
       // pre-pass: the utterances' mask tables (same Philox stream as b200mel_specaug_draw), in a
       // stream-ordered scratch buffer so that concurrent callers of one handle do not share state
       CU_CHECK(cudaMallocAsync(reinterpret_cast<void**>(&tmp_table),

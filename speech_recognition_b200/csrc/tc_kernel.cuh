@@ -47,7 +47,10 @@ constexpr int kTcSmemA = 10 * kTcBBytes;                       // 81920
 constexpr int kTcSmemOut = kTcSmemA + 10 * kTcStreamBytes;     // 168960
 constexpr int kTcOutPitch = 84;                                // floats per staged row (16-B aligned, conflict-free)
 constexpr int kTcSmemCtl = kTcSmemOut + kTcTileM * kTcOutPitch * 4;  // 211968
-constexpr int kTcSmemTotal = kTcSmemCtl + 256 + 1024;          // + control block + alignment slack
+constexpr int kTcSmemMask = kTcSmemCtl + 256;                  // SpecAugment tables of the CTA's tiles
+constexpr int kTcMaskTiles = 128;                              // ... at most this many tiles per CTA
+constexpr int kTcMaskEntries = 16;                             // ... and 8 masks (start, width) per utterance
+constexpr int kTcSmemTotal = kTcSmemMask + kTcMaskTiles * kTcMaskEntries * 4 + 1024;  // + alignment slack
 // Four warpgroups: MMA issuer (warp 0) + producers (warps 1-7), epilogue groups A and B (warps 8-11,
 // 12-15).  The launch allocates 128 registers per thread; setmaxnreg moves the producers' spare
 // registers to the epilogue (per SM sub-partition: 2 x 96 + 2 x 160 = 512).

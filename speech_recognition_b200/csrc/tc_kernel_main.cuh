@@ -40,16 +40,40 @@ __global__ void tc_eps_probe_kernel(float eps, float* out) { out[0] = tc_log_fas
             make_float4(tc_finish(A, eps, log_eps), tc_finish(B, eps, log_eps), tc_finish(C, eps, log_eps), \
                         tc_finish(D, eps, log_eps)))
 
+#if defined(TC_TRACE)
+// developer trace (experiments/trace_roles.py): clock64 stamps of CTA 0, [role][tile][event]
+__device__ long long g_tc_trace[4][32][8];
+#define TC_STAMP(ROLE, N, EV)                                                   \
+  if (blockIdx.x == 0 && (N) < 32) g_tc_trace[ROLE][N][EV] = clock64();
+__device__ __forceinline__ long long tc_clock_fenced() {
+  long long t;
+  asm volatile("mov.u64 %0, %%clock64;" : "=l"(t)::"memory");
+  return t;
+}
+#define TC_STAMP_F(ROLE, N, EV)                                                 \
+  if (blockIdx.x == 0 && (N) < 32) g_tc_trace[ROLE][N][EV] = tc_clock_fenced();
+#else
+#define TC_STAMP(ROLE, N, EV)
+#define TC_STAMP_F(ROLE, N, EV)
+#endif
+
 // SpecAugment on the thread's own staged row (data.py:286-288, 299-301): audio *= mask, so a masked
 // negative value becomes -0.0 exactly like the reference's multiply.  tb = (start, width) pairs,
 // frequency masks first.  Out of line: it runs once per tile and must not bloat the hot loop.
-__device__ __noinline__ void tc_mask_row(float* row, const int32_t* __restrict__ tb, int n_f, int n_t, int t) {
+__device__ __noinline__ void tc_mask_row(float* row, int32_t entry, int n_f, int n_t, int t, bool valid) {
+  // `entry` = table entry number `lane` of the row's utterance (fetched at the top of the tile); all
+  // 32 lanes call this, `valid` = the row is a real frame.  Multiplying by 0.0f keeps the sign like
+  // the reference's `audio *= mask`.  Measured (trace stamps): what this costs is not instructions but
+  // shared-memory round trips - the pipe is shared with the tensor core's operand fetch (~100 cycles
+  // per access while MMAs run) - so whole float4 groups, as few accesses as possible.  Wider batches
+  // of loads (8 groups in flight) were tried: the registers they need spill the epilogue's main loop.
   bool tm = false;
   for (int i = 0; i < n_t; ++i) {
-    const int s = __ldg(tb + 2 * (n_f + i)), w = __ldg(tb + 2 * (n_f + i) + 1);
+    const int s = __shfl_sync(0xffffffffu, entry, 2 * (n_f + i)), w = __shfl_sync(0xffffffffu, entry, 2 * (n_f + i) + 1);
     tm = tm || (t >= s && t < s + w);
   }
-  if (tm) {
+  if (tm && valid) {
+#pragma unroll 4
     for (int g = 0; g < 20; ++g) {
       float4 v = *reinterpret_cast<float4*>(row + 4 * g);
       v.x *= 0.0f; v.y *= 0.0f; v.z *= 0.0f; v.w *= 0.0f;
@@ -57,10 +81,78 @@ __device__ __noinline__ void tc_mask_row(float* row, const int32_t* __restrict__
     }
   }
   for (int i = 0; i < n_f; ++i) {
-    const int s = __ldg(tb + 2 * i), w = __ldg(tb + 2 * i + 1);
+    const int s = __shfl_sync(0xffffffffu, entry, 2 * i), w = __shfl_sync(0xffffffffu, entry, 2 * i + 1);
     const int e = s + w < 80 ? s + w : 80;
-    for (int m = s > 0 ? s : 0; m < e; ++m) row[m] *= 0.0f;
+    if (valid && !tm && e > s) {
+      const int g0 = s >> 2, g1 = (e + 3) >> 2;
+#pragma unroll 2
+      for (int g = g0; g < g1; ++g) {
+        float4 v = *reinterpret_cast<float4*>(row + 4 * g);
+        const int m = 4 * g;
+        v.x *= (m + 0 >= s && m + 0 < e) ? 0.0f : 1.0f;
+        v.y *= (m + 1 >= s && m + 1 < e) ? 0.0f : 1.0f;
+        v.z *= (m + 2 >= s && m + 2 < e) ? 0.0f : 1.0f;
+        v.w *= (m + 3 >= s && m + 3 < e) ? 0.0f : 1.0f;
+        *reinterpret_cast<float4*>(row + 4 * g) = v;
+      }
+    }
   }
+}
+
+// SpecAugment draws of the tiles of this CTA, by the 256 epilogue threads while they wait for the
+// first accumulators: raw Philox words first (one per thread), then one thread per tile turns them
+// into the reference's (start, width) table in draw order (common.cuh: specaug_draw_table).
+struct TcDrawArgs {
+  const int32_t* lengths;
+  int32_t* status;
+  uint64_t seed, first_utt;
+  int32_t n_masks_f, n_masks_t, sa_F, sa_T;
+  float sa_p;
+  int32_t tiles_per_utt, total_tiles;
+};
+__device__ __noinline__ void tc_draw_tables(int32_t* tab, const TcDrawArgs p, int etid) {
+  const TcDrawArgs& tp = p;
+  const int n_e = 2 * (p.n_masks_f + p.n_masks_t);
+  const int n_tiles = (tp.total_tiles - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x);
+  for (int k = etid; k < n_tiles * kTcMaskEntries; k += 256) {
+    const int i = k / kTcMaskEntries, d = k - i * kTcMaskEntries;
+    if (d < n_e) {
+      const int b = (static_cast<int>(blockIdx.x) + i * static_cast<int>(gridDim.x)) / tp.tiles_per_utt;
+      tab[k] = static_cast<int32_t>(specaug_raw_draw(p.seed, p.first_utt + static_cast<uint64_t>(b), static_cast<uint32_t>(d)));
+    }
+  }
+  tc::named_bar_sync(10, 256);
+  for (int i = etid; i < n_tiles; i += 256) {
+    const int b = (static_cast<int>(blockIdx.x) + i * static_cast<int>(gridDim.x)) / tp.tiles_per_utt;
+    const int32_t num_time = frames_of(__ldg(p.lengths + b), 320, 160);
+    int32_t* e = tab + i * kTcMaskEntries;
+    int bad = 0, o = 0;
+    for (int q = 0; q < p.n_masks_f; ++q) {
+      int32_t f = static_cast<int32_t>(static_cast<uint32_t>(e[o]) % static_cast<uint32_t>(p.sa_F));
+      const uint32_t u = static_cast<uint32_t>(e[o + 1]);
+      const int32_t range = 80 - f;
+      int32_t f0 = 0;
+      if (range <= 0) { bad = 1; f = 0; } else { f0 = static_cast<int32_t>(u % static_cast<uint32_t>(range)); }
+      e[o++] = f0;
+      e[o++] = f;
+    }
+    int32_t applied = 0;
+    const int32_t cap = static_cast<int32_t>(static_cast<float>(num_time) * p.sa_p);
+    for (int q = 0; q < p.n_masks_t; ++q) {
+      int32_t t = static_cast<int32_t>(static_cast<uint32_t>(e[o]) % static_cast<uint32_t>(p.sa_T));
+      const int32_t room = cap - applied;
+      t = t < room ? t : room;
+      applied += t;
+      const uint32_t u = static_cast<uint32_t>(e[o + 1]);
+      const int32_t range = num_time - t;
+      int32_t t0 = 0;
+      if (range <= 0) { bad = 1; t = 0; } else { t0 = static_cast<int32_t>(u % static_cast<uint32_t>(range)); }
+      e[o++] = t0;
+      e[o++] = t;
+    }
+    if (bad && p.status) atomicOr(p.status, 1);
+  }
+  tc::named_bar_sync(10, 256);
 }
 
 __device__ __noinline__ void tc_zero_row(float* row) {
@@ -79,14 +171,6 @@ __device__ __noinline__ void tc_produce_tile_slow(const short* __restrict__ pcm,
   }
 }
 
-#if defined(TC_TRACE)
-// developer trace (experiments/trace_roles.py): clock64 stamps of CTA 0, [role][tile][event]
-__device__ long long g_tc_trace[4][32][8];
-#define TC_STAMP(ROLE, N, EV)                                                   \
-  if (blockIdx.x == 0 && (N) < 32) g_tc_trace[ROLE][N][EV] = clock64();
-#else
-#define TC_STAMP(ROLE, N, EV)
-#endif
 
 // (utterance, tile within the utterance) of a tile index, advanced by the grid stride without a division
 struct TcTileIter {
@@ -409,6 +493,23 @@ __global__ void __launch_bounds__(kTcThreads, 1)
     const uint32_t bar_ready = 1 + wq, bar_free = 5 + wq;  // pair barriers (64 threads)
     bool pending = false;  // C == 1: the pair's previous TMA store may still be reading the staged rows
     bool issuer = false;   // this thread issued it (bulk async-groups are per thread)
+    int32_t* sMask = reinterpret_cast<int32_t*>(smem + kTcSmemMask);
+    if (n_masks > 0 && !p.mask_table) {
+      TcDrawArgs da;
+      da.lengths = p.lengths;
+      da.status = p.status;
+      da.seed = p.seed;
+      da.first_utt = p.first_utt;
+      da.n_masks_f = p.n_masks_f;
+      da.n_masks_t = p.n_masks_t;
+      da.sa_F = p.sa_F;
+      da.sa_T = p.sa_T;
+      da.sa_p = p.sa_p;
+      da.tiles_per_utt = tp.tiles_per_utt;
+      da.total_tiles = tp.total_tiles;
+      tc_draw_tables(sMask, da, etid);
+    }
+    int ti = 0;  // ordinal of the tile among this CTA's tiles (indexes the drawn tables)
     TcTileIter it;
     it.init(blockIdx.x, tp.tiles_per_utt);
     int32_t len_nxt = __ldg(p.lengths + it.b);
@@ -417,6 +518,13 @@ __global__ void __launch_bounds__(kTcThreads, 1)
       const int32_t len = len_nxt;  // fetched one tile ahead
       it.step(step_b, step_j, tp.tiles_per_utt);
       if (tile + gridDim.x < tp.total_tiles) len_nxt = __ldg(p.lengths + it.b);
+      // SpecAugment: lane i of every group-B warp fetches entry i of the utterance's mask table now
+      // (at most 16 masks on this path); it is consumed after the whole tile has been reduced
+      int32_t mask_entry = 0;
+      if (n_masks > 0 && group == 1 && lane < 2 * n_masks)
+        mask_entry = p.mask_table ? __ldg(p.mask_table + static_cast<size_t>(b) * 2 * n_masks + lane)
+                                  : sMask[ti * kTcMaskEntries + lane];
+      ++ti;
       const int n_fr = frames_of(len, 320, 160);
       const int t_first = j * tp.tout;  // first OUTPUT frame of this tile; row i holds frame t_first - halo + i
       const bool active = t_first < n_fr;
@@ -527,8 +635,7 @@ __global__ void __launch_bounds__(kTcThreads, 1)
           tc::named_bar_sync(bar_ready, 64);
           if (lane == 0 && wq == 0) { TC_STAMP(3, n, 4) }
           TC_MEL_SHARED_B;
-          if (n_masks > 0 && t_row >= 0 && t_row < n_fr)
-            tc_mask_row(out_row, p.mask_table + static_cast<size_t>(b) * 2 * n_masks, p.n_masks_f, p.n_masks_t, t_row);
+          if (n_masks > 0) tc_mask_row(out_row, mask_entry, p.n_masks_f, p.n_masks_t, t_row, t_row >= 0 && t_row < n_fr);
         }
 #undef TC_LOAD_CHUNK
 #undef TC_RADIX_STEP
@@ -617,8 +724,18 @@ inline TcEncodeTiledFn tc_encode_fn() {
   return fn;
 }
 
-// Host launcher.  Returns 0 on success.  With SpecAugment enabled kp.mask_table must be set (the
-// API layer draws it with specaug_draw_kernel when the caller passes none).
+// SpecAugment without a caller-supplied table: the kernel draws the tables of a CTA's tiles itself when
+// they fit its shared-memory table (<= 8 masks, <= 128 tiles per CTA); otherwise the API layer runs
+// specaug_draw_from_lengths_kernel as a pre-pass and passes the table.
+inline bool tc_draws_in_kernel(const KernelParams& kp, int sm_count) {
+  const int halo = kp.C == 3 ? 2 : 0, tout = kTcTileM - halo;
+  const int64_t total = ((kp.t_max + tout - 1) / tout) * kp.batch;
+  const int64_t grid = total < sm_count ? total : sm_count;
+  return 2 * (kp.n_masks_f + kp.n_masks_t) <= kTcMaskEntries && grid > 0 && (total + grid - 1) / grid <= kTcMaskTiles;
+}
+
+// Host launcher.  Returns 0 on success.  With SpecAugment enabled and no kp.mask_table the kernel
+// draws the tables itself: the caller checks tc_draws_in_kernel() first.
 inline int tc_launch(const TcPlan& tc, const KernelParams& kp, int sm_count, cudaStream_t st) {
   TcParams tp;
   tp.b_image = tc.d_b;

@@ -188,6 +188,29 @@ def test_delta_and_masks_fused(fe_mod, kernel):
         assert np.all(full[i, t:] == 0.0) and not np.any(np.signbit(full[i, t:]))
 
 
+@pytest.mark.parametrize("m_F,m_T", [(2, 2), (5, 4), (8, 8)])
+def test_tc_mask_paths_agree_with_the_oracle_draws(fe_mod, m_F, m_T):
+    """The tensor-core kernel draws the tables itself for <= 8 masks per utterance and takes them
+    from a pre-pass kernel for 9..16 (the library's maximum): both must apply exactly the oracle's
+    draws (C = 1, the TMA-store path)."""
+    sa = dict(enable=True, W=None, F=11, m_F=m_F, T=40, p=1.0, m_T=m_T)
+    lengths = [48000, 31000, 16500, 20000]
+    batch = np.zeros((4, 48000), np.int16)
+    for i, n in enumerate(lengths):
+        batch[i, :n] = noise_int16(n, 60 + i)
+    base, nf = fe_mod.FeatureFrontend("log-mel-spectrogram", **LIBRI)(dev(batch), lengths=lengths, kernel="tc")
+    fe = fe_mod.FeatureFrontend("log-mel-spectrogram", **LIBRI, spec_augment=sa)
+    got, _ = fe(dev(batch), lengths=lengths, seed=7, first_utterance_id=123, kernel="auto")
+    base, got, nf = base.cpu().numpy(), got.cpu().numpy(), nf.cpu().numpy()
+    for i in range(4):
+        t = int(nf[i])
+        tbl = O.specaug_draw_masks(t, 80, 11, m_F, 40, 1.0, m_T, seed=7, utterance_id=123 + i)
+        want = O.spec_augment_apply(base[i, :t], tbl[:m_F], tbl[m_F:])
+        assert np.array_equal(got[i, :t], want)          # same kernel, same base features
+        assert np.array_equal(np.signbit(got[i, :t]), np.signbit(want))
+        assert np.all(got[i, t:] == 0.0)
+
+
 def test_masks_are_sharding_invariant(fe_mod):
     """Masks are a pure function of (seed, global utterance id): any split of the batch over
     ranks gives the same result (BASELINE config 3)."""
