@@ -20,7 +20,7 @@ t = np.array(buf[:]).reshape(4, 32, 8)
 t0 = t[t > 0].min()
 names = ["P ", "M ", "EA", "EB"]
 ev = {0: ["start", "w0", "w1", "w2", "w3", "arr_w4", "done", "arr_w7"], 1: ["top", "afull0", "pre_accE", "accE_ok", "committed", "afull1_ok"],
-      2: ["top", "accfull", "released", "loopend", "", "done", "m_start", "m_time"], 3: ["top", "accfull", "released", "loopend", "ready", "done", "m_built", "m_end"]}
+      2: ["top", "accfull", "released", "loopend", "", "done", "P1w3", "P1w5"], 3: ["top", "accfull", "released", "loopend", "ready", "done", "P1w6", "P1w7"]}
 print("kernel: top=%d setup_done=%d dep_wait_done=%d teardown=%d" % tuple(t[1, 31, e] - t0 for e in range(4)))
 t[1, 31, :] = 0
 for n in list(range(0, 2)) + list(range(9, 12)) + list(range(20, 21)):

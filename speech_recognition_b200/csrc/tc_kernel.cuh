@@ -50,7 +50,10 @@ constexpr int kTcSmemCtl = kTcSmemOut + kTcTileM * kTcOutPitch * 4;  // 211968
 constexpr int kTcSmemMask = kTcSmemCtl + 256;                  // SpecAugment tables of the CTA's tiles
 constexpr int kTcMaskTiles = 128;                              // ... at most this many tiles per CTA
 constexpr int kTcMaskEntries = 16;                             // ... and 8 masks (start, width) per utterance
-constexpr int kTcSmemTotal = kTcSmemMask + kTcMaskTiles * kTcMaskEntries * 4 + 1024;  // + alignment slack
+constexpr int kTcSmemWalk = kTcSmemMask + kTcMaskTiles * kTcMaskEntries * 4;  // one work cursor per warp (16 x 32 B)
+constexpr int kTcSmemList = kTcSmemWalk + 512;                 // the CTA's tiles: (utterance, tile, length, block offset)
+constexpr int kTcListTiles = 512;                              // ... at most this many per CTA and launch
+constexpr int kTcSmemTotal = kTcSmemList + kTcListTiles * 16 + 1024;  // + alignment slack
 // Four warpgroups: MMA issuer (warp 0) + producers (warps 1-7), epilogue groups A and B (warps 8-11,
 // 12-15).  The launch allocates 128 registers per thread; setmaxnreg moves the producers' spare
 // registers to the epilogue (per SM sub-partition: 2 x 96 + 2 x 160 = 512).

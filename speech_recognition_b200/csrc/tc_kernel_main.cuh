@@ -10,7 +10,9 @@ struct TcCtl {
   uint64_t acc_full;    // tcgen05.commit -> epilogue: the 5 accumulators of this tile are complete
   uint64_t acc_empty;   // epilogue (256 arrivals) -> MMA: this tile's TMEM slots may be overwritten
   uint64_t b_full;      // TMA bulk copy -> MMA: the B operand image has landed in shared memory
+  uint64_t list_full;   // epilogue warps (8 arrivals) -> everybody: the CTA's tile list is complete
   uint32_t tmem_base;
+  int32_t n_tiles;      // length of the tile list
 };
 
 // log(mel + eps): one MUFU.LG2 + one FMUL (abs error ~ 2^-22 * |log|; mel + eps >= eps is a normal
@@ -99,32 +101,170 @@ __device__ __noinline__ void tc_mask_row(float* row, int32_t entry, int n_f, int
   }
 }
 
-// SpecAugment draws of the tiles of this CTA, by the 256 epilogue threads while they wait for the
-// first accumulators: raw Philox words first (one per thread), then one thread per tile turns them
-// into the reference's (start, width) table in draw order (common.cuh: specaug_draw_table).
+__device__ __noinline__ void tc_zero_row(float* row) {
+  for (int g = 0; g < 20; ++g) *reinterpret_cast<float4*>(row + 4 * g) = make_float4(0.f, 0.f, 0.f, 0.f);
+}
+
+// Unaligned utterance start (ragged offsets that are not a multiple of 8 samples): element-wise
+// producer, one group at a time.  Rare path, kept out of line.
+__device__ __noinline__ void tc_produce_tile_slow(const short* __restrict__ pcm, int64_t s_begin, int32_t len,
+                                                  uint8_t* sA, int ptid) {
+  for (int g = ptid; g < 516; g += kTcProducerThreads) {
+    uint4 raw[5];
+#pragma unroll
+    for (int q = 0; q < 5; ++q) raw[q] = tc_load8_slow(pcm, s_begin + 40 * g + 8 * q, len);
+    tc_produce_group(raw[0], raw[1], raw[2], raw[3], raw[4], sA, g);
+  }
+}
+
+
+// ---------------------------------------------------------------------------------------------
+// Work partition.  A tile (128 rows of one utterance) is ACTIVE when it holds at least one real
+// frame below t_max.  The active tiles of the batch, in (utterance, tile) order, are split into
+// contiguous equal ranges over the CTAs, so that ragged batches stay balanced (round-robin over all
+// tiles left some CTAs with 40 % more real work than the average).  The rows behind an utterance's
+// last active tile are pure padding: they are zero-filled at the end of the kernel by every warp, in
+// 32-row blocks split the same way.  Each warp finds its range itself from the lengths (one pass,
+// eight utterances per lane, shuffles): no pre-pass kernel, no global work counter.
+// ---------------------------------------------------------------------------------------------
+struct TcWalk {  // warp-uniform cursor over a contiguous range of units (active tiles, or padding blocks)
+  int32_t b, j, na;  // current utterance, unit inside it, number of units of that utterance
+  int32_t left;      // units left in the range, the current one included
+  int32_t len, len_nb;  // length of utterance b; of utterance b + 1 (fetched one utterance ahead)
+};
+__device__ __forceinline__ int32_t tc_nact(int32_t len, int32_t t_max, int32_t tout) {
+  int32_t f = frames_of(len, 320, 160);
+  f = f < t_max ? f : t_max;
+  return (f + tout - 1) / tout;
+}
+template <bool kPad>
+__device__ __forceinline__ int32_t tc_units(int32_t len, int32_t t_max, int32_t tout) {
+  const int32_t na = tc_nact(len, t_max, tout);
+  if (!kPad) return na;
+  const int32_t r = t_max - na * tout;  // rows behind the last active tile
+  return r > 0 ? (r + 31) >> 5 : 0;
+}
+// Range number `part` of `n_parts`.  All 32 lanes call this.  n_frames_out (one warp of the grid only):
+// also report every utterance's frame count, and flag the zero-frame utterances the reference's
+// SpecAugment would have raised on (data.py:297: maxval <= minval).
+template <bool kPad>
+__device__ __forceinline__ void tc_walk_begin(TcWalk* dst, const int32_t* __restrict__ lengths, int32_t batch, int32_t t_max,
+                                           int32_t tout, uint32_t part, uint32_t n_parts, int lane, int32_t* n_frames_out,
+                                           int32_t* status_if_empty) {
+  // (the result goes to the warp's slot in shared memory: a reference to a local object would put
+  //  the caller's cursor on the stack, and the callers run under setmaxnreg)
+  TcWalk w;
+  long long total = 0;
+  for (int base = 0; base < batch; base += 256) {
+    int32_t s = 0;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const int b = base + 8 * lane + k;
+      if (b < batch) {
+        const int32_t l = __ldg(lengths + b);
+        s += tc_units<kPad>(l, t_max, tout);
+        if (n_frames_out || status_if_empty) {
+          const int32_t f = frames_of(l, 320, 160);
+          if (n_frames_out) n_frames_out[b] = f;
+          if (f == 0 && status_if_empty) atomicOr(status_if_empty, 1);
+        }
+      }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    total += s;
+  }
+  const long long a0 = (total * part) / n_parts, a1 = (total * (part + 1)) / n_parts;
+  w.left = static_cast<int32_t>(a1 - a0);
+  w.b = 0;
+  w.j = 0;
+  w.na = 0;
+  w.len = 0;
+  w.len_nb = 0;
+  if (w.left <= 0) {
+    if (lane == 0) *dst = w;
+    __syncwarp();
+    return;
+  }
+  long long acc = 0;
+  for (int base = 0; base < batch; base += 256) {
+    int32_t c[8], s = 0;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const int b = base + 8 * lane + k;
+      c[k] = b < batch ? tc_units<kPad>(__ldg(lengths + b), t_max, tout) : 0;
+      s += c[k];
+    }
+    int32_t incl = s;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int32_t v = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += v;
+    }
+    const int32_t tot = __shfl_sync(0xffffffffu, incl, 31);
+    if (acc + tot <= a0) {
+      acc += tot;
+      continue;
+    }
+    const uint32_t hit = __ballot_sync(0xffffffffu, acc + incl > a0);
+    const int src = __ffs(hit) - 1;
+    int32_t bb = 0, jj = 0;
+    long long r = a0 - (acc + incl - s);  // (meaningful in lane `src`)
+    bool found = false;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      if (!found && r < c[k]) {
+        bb = base + 8 * lane + k;
+        jj = static_cast<int32_t>(r);
+        found = true;
+      }
+      r -= c[k];
+    }
+    w.b = __shfl_sync(0xffffffffu, bb, src);
+    w.j = __shfl_sync(0xffffffffu, jj, src);
+    break;
+  }
+  w.len = __shfl_sync(0xffffffffu, __ldg(lengths + w.b), 0);
+  w.na = tc_units<kPad>(w.len, t_max, tout);
+  w.len_nb = w.b + 1 < batch ? __ldg(lengths + w.b + 1) : 0;
+  if (lane == 0) *dst = w;
+  __syncwarp();
+}
+// next unit of the range (all lanes).  No load on the critical path: the next utterance's length was
+// fetched when the current utterance was entered.
+template <bool kPad>
+__device__ __forceinline__ void tc_walk_step(TcWalk& w, const int32_t* __restrict__ lengths, int32_t batch, int32_t t_max,
+                                             int32_t tout) {
+  if (--w.left <= 0) return;
+  if (++w.j < w.na) return;
+  w.j = 0;
+  do {  // (utterances without units are skipped; left > 0 guarantees that one with units follows)
+    ++w.b;
+    w.len = __shfl_sync(0xffffffffu, w.len_nb, 0);
+    w.len_nb = w.b + 1 < batch ? __ldg(lengths + w.b + 1) : 0;
+    w.na = tc_units<kPad>(w.len, t_max, tout);
+  } while (w.na == 0 && w.b + 1 < batch);
+}
+
+// SpecAugment draws of this CTA's tiles, by the 256 epilogue threads while they wait for the first
+// accumulators: raw Philox words first (one per thread), then one thread per tile turns them into
+// the reference's (start, width) table in draw order (common.cuh: specaug_draw_table).
 struct TcDrawArgs {
-  const int32_t* lengths;
   int32_t* status;
   uint64_t seed, first_utt;
   int32_t n_masks_f, n_masks_t, sa_F, sa_T;
   float sa_p;
-  int32_t tiles_per_utt, total_tiles;
 };
-__device__ __noinline__ void tc_draw_tables(int32_t* tab, const TcDrawArgs p, int etid) {
-  const TcDrawArgs& tp = p;
+__device__ __noinline__ void tc_draw_tables(int32_t* tab, const TcDrawArgs p, const int4* list, int n_tiles, int etid) {
   const int n_e = 2 * (p.n_masks_f + p.n_masks_t);
-  const int n_tiles = (tp.total_tiles - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x);
   for (int k = etid; k < n_tiles * kTcMaskEntries; k += 256) {
     const int i = k / kTcMaskEntries, d = k - i * kTcMaskEntries;
-    if (d < n_e) {
-      const int b = (static_cast<int>(blockIdx.x) + i * static_cast<int>(gridDim.x)) / tp.tiles_per_utt;
-      tab[k] = static_cast<int32_t>(specaug_raw_draw(p.seed, p.first_utt + static_cast<uint64_t>(b), static_cast<uint32_t>(d)));
-    }
+    if (d < n_e)
+      tab[k] = static_cast<int32_t>(specaug_raw_draw(p.seed, p.first_utt + static_cast<uint64_t>(list[i].x), static_cast<uint32_t>(d)));
   }
   tc::named_bar_sync(10, 256);
   for (int i = etid; i < n_tiles; i += 256) {
-    const int b = (static_cast<int>(blockIdx.x) + i * static_cast<int>(gridDim.x)) / tp.tiles_per_utt;
-    const int32_t num_time = frames_of(__ldg(p.lengths + b), 320, 160);
+    const int32_t num_time = frames_of(list[i].z, 320, 160);
     int32_t* e = tab + i * kTcMaskEntries;
     int bad = 0, o = 0;
     for (int q = 0; q < p.n_masks_f; ++q) {
@@ -155,40 +295,6 @@ __device__ __noinline__ void tc_draw_tables(int32_t* tab, const TcDrawArgs p, in
   tc::named_bar_sync(10, 256);
 }
 
-__device__ __noinline__ void tc_zero_row(float* row) {
-  for (int g = 0; g < 20; ++g) *reinterpret_cast<float4*>(row + 4 * g) = make_float4(0.f, 0.f, 0.f, 0.f);
-}
-
-// Unaligned utterance start (ragged offsets that are not a multiple of 8 samples): element-wise
-// producer, one group at a time.  Rare path, kept out of line.
-__device__ __noinline__ void tc_produce_tile_slow(const short* __restrict__ pcm, int64_t s_begin, int32_t len,
-                                                  uint8_t* sA, int ptid) {
-  for (int g = ptid; g < 516; g += kTcProducerThreads) {
-    uint4 raw[5];
-#pragma unroll
-    for (int q = 0; q < 5; ++q) raw[q] = tc_load8_slow(pcm, s_begin + 40 * g + 8 * q, len);
-    tc_produce_group(raw[0], raw[1], raw[2], raw[3], raw[4], sA, g);
-  }
-}
-
-
-// (utterance, tile within the utterance) of a tile index, advanced by the grid stride without a division
-struct TcTileIter {
-  int b, j;
-  __device__ __forceinline__ void init(int t, int tiles_per_utt) {
-    b = t / tiles_per_utt;
-    j = t - b * tiles_per_utt;
-  }
-  __device__ __forceinline__ void step(int step_b, int step_j, int tiles_per_utt) {
-    b += step_b;
-    j += step_j;
-    if (j >= tiles_per_utt) {
-      j -= tiles_per_utt;
-      ++b;
-    }
-  }
-};
-
 template <int C>
 __global__ void __launch_bounds__(kTcThreads, 1)
     tc_frontend_kernel(const KernelParams p, const TcParams tp, const __grid_constant__ CUtensorMap out_map) {
@@ -214,6 +320,7 @@ __global__ void __launch_bounds__(kTcThreads, 1)
     }
     tc::mbar_init(&ctl->acc_full, 1);
     tc::mbar_init(&ctl->acc_empty, 256);
+    tc::mbar_init(&ctl->list_full, 8);
     tc::fence_mbar_init();
     // B operand (80 KB, constant): two bulk copies by the TMA engine, only the MMA issuer waits for
     // them - producers and epilogue warps start on the first tile at once
@@ -222,19 +329,30 @@ __global__ void __launch_bounds__(kTcThreads, 1)
     tc::bulk_copy_g2s(tc::smem_u32(sB) + 5 * kTcBBytes, tp.b_image + 5 * kTcBBytes, 5 * kTcBBytes, &ctl->b_full);
   }
   if (warp == kTcMmaWarp) tc::tmem_alloc(&ctl->tmem_base, 512);
-  const int step_b = gridDim.x / tp.tiles_per_utt, step_j = gridDim.x - step_b * tp.tiles_per_utt;
+  const int32_t t_max32 = p.t_max < 0x7fffffff ? static_cast<int32_t>(p.t_max) : 0x7fffffff;
+  TcWalk* swk = reinterpret_cast<TcWalk*>(smem + kTcSmemWalk) + warp;  // this warp's work cursor slot
+  // The CTA's tiles in processing order, (utterance, tile, length, 8-sample block offset or bit 31 =
+  // "not 16-byte aligned"): built by the epilogue warps while they wait for the first accumulators,
+  // read by every role (one 16-byte broadcast load per tile instead of cursor arithmetic).
+  int4* sList = reinterpret_cast<int4*>(smem + kTcSmemList);
+  const bool pcm_al = (reinterpret_cast<uintptr_t>(p.pcm) & 15) == 0;
+  auto fetch_blk = [&](int bt) -> uint32_t {
+    const int64_t o = p.offsets ? __ldg(p.offsets + bt) : static_cast<int64_t>(bt) * p.row_stride;
+    return (pcm_al && (o & 7) == 0) ? static_cast<uint32_t>(o >> 3) : 0x80000000u;
+  };
   if (tid == 64 && p.offsets == nullptr && (reinterpret_cast<uintptr_t>(p.pcm) & 15) == 0 && (p.row_stride & 7) == 0) {
     // Pull the PCM range of this CTA's first tile into L2 before anything else: its loads otherwise
-    // start only after the (cold) length fetch.  The range is bounded by the row, not by the utterance
-    // length (not known yet); an L2 prefetch has no architectural effect, so it may precede the
-    // dependency wait below.
-    TcTileIter it;
-    it.init(blockIdx.x, tp.tiles_per_utt);
-    int64_t s0 = 160 * static_cast<int64_t>(it.j * tp.tout - tp.halo), s1 = s0 + 129 * 160;
+    // start only after the (cold) pass over the lengths.  The tile is guessed as if every tile of the
+    // batch were active (exact for a batch of full-length utterances) and the range is bounded by the
+    // row, not by the utterance; an L2 prefetch has no architectural effect, so a wrong guess is
+    // harmless and it may precede the dependency wait below.
+    const int t0 = static_cast<int>((static_cast<long long>(tp.total_tiles) * blockIdx.x) / gridDim.x);
+    const int b0 = t0 / tp.tiles_per_utt, j0 = t0 - b0 * tp.tiles_per_utt;
+    int64_t s0 = 160 * static_cast<int64_t>(j0 * tp.tout - tp.halo), s1 = s0 + 129 * 160;
     if (s0 < 0) s0 = 0;
     if (s1 > p.row_stride) s1 = p.row_stride;
     if (s1 > s0)
-      tc::prefetch_l2(static_cast<const int16_t*>(p.pcm) + static_cast<int64_t>(it.b) * p.row_stride + s0,
+      tc::prefetch_l2(static_cast<const int16_t*>(p.pcm) + static_cast<int64_t>(b0) * p.row_stride + s0,
                       static_cast<uint32_t>(2 * (s1 - s0)));
   }
   tc::tc_fence_before();
@@ -265,23 +383,6 @@ __global__ void __launch_bounds__(kTcThreads, 1)
     uint32_t ph[3];
 #pragma unroll
     for (int i = 0; i < 3; ++i) ph[i] = tc_stream_offset(ptid + kTcProducerThreads * i);
-    // (length, offset) of the utterances of this CTA's next two tiles, fetched ahead of use.  Offsets
-    // are kept in 8-sample blocks (bit 31 = "not 16-byte aligned": such utterances take the slow path).
-    const bool pcm_al = (reinterpret_cast<uintptr_t>(p.pcm) & 15) == 0;
-    auto fetch_len = [&](int t, int bt) -> int32_t { return t < tp.total_tiles ? __ldg(p.lengths + bt) : 0; };
-    auto fetch_blk = [&](int t, int bt) -> uint32_t {
-      if (t >= tp.total_tiles) return 0x80000000u;
-      const int64_t o = p.offsets ? __ldg(p.offsets + bt) : static_cast<int64_t>(bt) * p.row_stride;
-      return (pcm_al && (o & 7) == 0) ? static_cast<uint32_t>(o >> 3) : 0x80000000u;
-    };
-    TcTileIter it0, it1, it2;  // this tile, the CTA's next one, the one after
-    it0.init(blockIdx.x, tp.tiles_per_utt);
-    it1 = it0;
-    it1.step(step_b, step_j, tp.tiles_per_utt);
-    it2 = it1;
-    it2.step(step_b, step_j, tp.tiles_per_utt);
-    int32_t len1 = fetch_len(blockIdx.x, it0.b), len2 = fetch_len(blockIdx.x + gridDim.x, it1.b);
-    uint32_t bb1 = fetch_blk(blockIdx.x, it0.b), bb2 = fetch_blk(blockIdx.x + gridDim.x, it1.b);
     const uint4* pcm16 = reinterpret_cast<const uint4*>(p.pcm);
     uint32_t w[3][20];  // this thread's groups: raw words (two samples each), XOR-ed in place before use
     bool preloaded = false;
@@ -295,34 +396,25 @@ __global__ void __launch_bounds__(kTcThreads, 1)
     w[I][4 * q + 2] = v.z;                                                                             \
     w[I][4 * q + 3] = v.w;                                                                             \
   }
-    for (int tile = blockIdx.x; tile < tp.total_tiles; tile += gridDim.x) {
-      const int b = it0.b, j = it0.j, jn = it1.j;
-      const int32_t len = len1;
-      const uint32_t bb = bb1;
-      const int nx = tile + gridDim.x;  // next tile of this CTA: (len1, bb1) after the shift
-      len1 = len2;
-      bb1 = bb2;
-      len2 = fetch_len(nx + gridDim.x, it2.b);
-      bb2 = fetch_blk(nx + gridDim.x, it2.b);
-      it0 = it1;
-      it1 = it2;
-      it2.step(step_b, step_j, tp.tiles_per_utt);
-      // next tile: first block, clamp range (all in absolute 8-sample blocks; requires < 2^31 blocks)
-      const bool next_ok = !(bb1 & 0x80000000u) && jn * tp.tout < frames_of(len1, 320, 160);
-      const int32_t nb_lo = static_cast<int32_t>(bb1), nb_hi = nb_lo + (len1 >> 3) - 1;
-      const int32_t nb_0 = nb_lo + 20 * (jn * tp.tout - tp.halo);
+    if (!tc::mbar_wait(&ctl->list_full, 0)) timed_out = true;
+    const int n_tiles = ctl->n_tiles;
+    // Register budget: the 60 raw words of the NEXT tile are live across the top of the loop, so
+    // nothing about the tiles is carried in registers - every use re-reads the list entry.
+    // next tile: first block and clamp range, all in absolute 8-sample blocks (< 2^31 blocks)
+#define TC_NEXT_RANGE()                                                                           \
+  const int4 nxt = sList[ti + 1];                                                                 \
+  const int32_t nb_lo = nxt.w, nb_hi = nb_lo + (nxt.z >> 3) - 1;                                  \
+  const int32_t nb_0 = nb_lo + 20 * (nxt.y * tp.tout - tp.halo);
+    for (int ti = 0; ti < n_tiles; ++ti) {
+      const bool next_ok = ti + 1 < n_tiles && sList[ti + 1].w >= 0;  // (bit 31 = unaligned: slow path)
       if (next_ok && ptid == kTcProducerThreads - 1) {
         // ask the TMA engine to pull the next tile's PCM range into L2
+        TC_NEXT_RANGE()
         const int32_t q0 = nb_0 < nb_lo ? nb_lo : nb_0;
         const int32_t q1 = nb_0 + 129 * 20 - 1 < nb_hi ? nb_0 + 129 * 20 - 1 : nb_hi;
         if (q1 >= q0) tc::prefetch_l2(pcm16 + q0, 16u * (q1 - q0 + 1));
       }
-      const int n_fr = frames_of(len, 320, 160);
-      if (j * tp.tout >= n_fr) {  // nothing but padding: the epilogue zero-fills
-        preloaded = false;
-        continue;
-      }
-      const int32_t s_begin = 160 * (j * tp.tout - tp.halo);
+      const uint32_t bb = static_cast<uint32_t>(sList[ti].w);
       const uint32_t par = (n - 1) & 1;
       if (!(bb & 0x80000000u)) {
         // Every frame t < n_fr ends at a multiple of 8 samples <= len, so clamping the 8-sample
@@ -330,8 +422,9 @@ __global__ void __launch_bounds__(kTcThreads, 1)
         // only feed rows that the epilogue zero-fills (t >= n_fr) or drops (t < 0).
         if (ptid == 0) { TC_STAMP(0, n, 0) }
         if (!preloaded) {
-          const int32_t b_lo = static_cast<int32_t>(bb), b_hi = b_lo + (len >> 3) - 1;  // n_fr >= 1: len >= 320
-          const int32_t b_0 = b_lo + (s_begin >> 3);
+          const int4 cur = sList[ti];
+          const int32_t b_lo = cur.w, b_hi = b_lo + (cur.z >> 3) - 1;  // n_fr >= 1: len >= 320
+          const int32_t b_0 = b_lo + 20 * (cur.y * tp.tout - tp.halo);
           TC_LOAD_GROUP(0, b_0, b_lo, b_hi)
           TC_LOAD_GROUP(1, b_0, b_lo, b_hi)
           if (third) { TC_LOAD_GROUP(2, b_0, b_lo, b_hi) }
@@ -358,6 +451,10 @@ __global__ void __launch_bounds__(kTcThreads, 1)
         tc::fence_async_smem();  // generic-proxy writes -> visible to the tensor core (async proxy)
         tc::mbar_arrive(&ctl->a_full[0]);
         if (ptid == 0) { TC_STAMP(0, n, 3) }
+        if (ptid == 64) { TC_STAMP(2, n, 6) }
+        if (ptid == 128) { TC_STAMP(2, n, 7) }
+        if (ptid == 160) { TC_STAMP(3, n, 6) }
+        if (ptid == 223) { TC_STAMP(3, n, 7) }
         // ---- phase 2: residues 3-4, then reload the registers with the next tile's PCM
         if (n > 0 && !timed_out && !tc::mbar_wait(&ctl->a_empty[1], par)) timed_out = true;
         if (ptid == 0) { TC_STAMP(0, n, 4) }
@@ -376,6 +473,7 @@ __global__ void __launch_bounds__(kTcThreads, 1)
         // the registers are free: start loading the next tile's PCM (its range is in L2 by now).
         // After the fence on purpose - the fence waits for this thread's outstanding loads.
         if (next_ok) {
+          TC_NEXT_RANGE()
           TC_LOAD_GROUP(0, nb_0, nb_lo, nb_hi)
           TC_LOAD_GROUP(1, nb_0, nb_lo, nb_hi)
           if (third) { TC_LOAD_GROUP(2, nb_0, nb_lo, nb_hi) }
@@ -385,14 +483,16 @@ __global__ void __launch_bounds__(kTcThreads, 1)
       } else {
         for (int r = 0; r < 2; ++r)
           if (n > 0 && !timed_out && !tc::mbar_wait(&ctl->a_empty[r], par)) timed_out = true;
-        const int64_t base = p.offsets ? p.offsets[b] : static_cast<int64_t>(b) * p.row_stride;
-        tc_produce_tile_slow(reinterpret_cast<const short*>(p.pcm) + base, s_begin, len, sA, ptid);
+        const int4 cur = sList[ti];
+        const int64_t base = p.offsets ? p.offsets[cur.x] : static_cast<int64_t>(cur.x) * p.row_stride;
+        tc_produce_tile_slow(reinterpret_cast<const short*>(p.pcm) + base, 160 * (cur.y * tp.tout - tp.halo), cur.z, sA, ptid);
         tc::fence_async_smem();
         for (int r = 0; r < 2; ++r) tc::mbar_arrive(&ctl->a_full[r]);
         preloaded = false;
       }
       ++n;
     }
+#undef TC_NEXT_RANGE
 #undef TC_LOAD_GROUP
   } else if (warp == 0) {
     // ======================= MMA ISSUER (one thread of warp 0) ==================================
@@ -401,31 +501,16 @@ __global__ void __launch_bounds__(kTcThreads, 1)
     // as the youngest warp it was starved by the epilogue warps (96 instead of 60 cycles per MMA).
     tc::setmaxnreg_dec<kTcRegsProducer>();
     if (tc::elect_one()) {
-      uint32_t n = 0;
+      // the issuer only needs the NUMBER of tiles of this CTA (every tile of the list is active)
+      if (!tc::mbar_wait(&ctl->list_full, 0)) timed_out = true;
+      const uint32_t n_tiles = static_cast<uint32_t>(ctl->n_tiles);
       const uint32_t idesc = tc::make_idesc_f16(128, 64);
       const uint64_t a_base = tc::make_smem_desc(tc::smem_u32(sA), 16, 512, tc::kLayoutSw64);
       const uint64_t b_base = tc::make_smem_desc(tc::smem_u32(sB), 16, 1024, tc::kLayoutSw128);
       const uint32_t a_lo0 = static_cast<uint32_t>(a_base), a_hi = static_cast<uint32_t>(a_base >> 32);
       const uint32_t b_lo0 = static_cast<uint32_t>(b_base), b_hi = static_cast<uint32_t>(b_base >> 32);
       if (!tc::mbar_wait(&ctl->b_full, 0)) timed_out = true;
-      // "is this tile active" is evaluated one tile ahead, while the tensor pipe is busy with queued
-      // MMAs, so that the issuing thread has nothing to do between two tiles
-      auto tile_len = [&](int t, int bt) -> int32_t { return t < tp.total_tiles ? __ldg(p.lengths + bt) : 0; };
-      auto tile_active = [&](int t, int jt, int32_t len_t) -> bool {
-        return t < tp.total_tiles && jt * tp.tout < frames_of(len_t, 320, 160);
-      };
-      TcTileIter it;  // the CTA's NEXT tile inside the loop
-      it.init(blockIdx.x, tp.tiles_per_utt);
-      bool cur_active = tile_active(blockIdx.x, it.j, tile_len(blockIdx.x, it.b));
-      for (int tile = blockIdx.x; tile < tp.total_tiles; tile += gridDim.x) {
-        const int nx = tile + gridDim.x;
-        it.step(step_b, step_j, tp.tiles_per_utt);
-        if (!cur_active) {
-          cur_active = tile_active(nx, it.j, tile_len(nx, it.b));
-          continue;
-        }
-        const int32_t len_n = tile_len(nx, it.b);  // consumed after the MMAs of residue 2 are queued
-        bool nxt_active = false;
+      for (uint32_t n = 0; n < n_tiles; ++n) {
 #pragma unroll 1
         for (int r = 0; r < 5; ++r) {
           if (r == 0) {
@@ -460,16 +545,11 @@ __global__ void __launch_bounds__(kTcThreads, 1)
           }
           // commits only at the two hand-over points: a commit between residues drains the tensor
           // pipe (measured: ~300 cycles per commit)
-          if (r == 2) {
-            tc::umma_commit(&ctl->a_empty[0]);  // the streams of residues 0-2 may be refilled
-            nxt_active = tile_active(nx, it.j, len_n);
-          }
+          if (r == 2) tc::umma_commit(&ctl->a_empty[0]);  // the streams of residues 0-2 may be refilled
         }
         tc::umma_commit(&ctl->a_empty[1]);
         tc::umma_commit(&ctl->acc_full);
         TC_STAMP(1, n, 4)
-        cur_active = nxt_active;
-        ++n;
       }
     }
     __syncwarp();
@@ -494,9 +574,85 @@ __global__ void __launch_bounds__(kTcThreads, 1)
     bool pending = false;  // C == 1: the pair's previous TMA store may still be reading the staged rows
     bool issuer = false;   // this thread issued it (bulk async-groups are per thread)
     int32_t* sMask = reinterpret_cast<int32_t*>(smem + kTcSmemMask);
+    // the first epilogue warp of the grid also reports the frame counts, and flags the zero-frame
+    // utterances on which the reference's time-mask draw raises
+    const bool reporter = blockIdx.x == 0 && warp == 8;
+    // (the cursor lives in shared memory: the epilogue's main loop has no registers to spare)
+    {
+      // ---- the CTA's tile list, in one pass over the lengths: thread (warp e, lane l) owns utterance
+      //      256 c + 8 l + e of every chunk c of 256; a warp scan of the per-lane counts gives the
+      //      index of its first active tile, and it writes those of its tiles that fall into this
+      //      CTA's range.  Ready ~one L2 round trip after the kernel starts. ----
+      const int ew = warp - 8;
+      int32_t* nfo = reporter ? p.n_frames : nullptr;
+      int32_t* sfe = (reporter && p.n_masks_t > 0) ? p.status : nullptr;
+      long long total = 0;
+      int32_t c[8], mylen = 0;
+      for (int base = 0; base < p.batch; base += 256) {
+        int32_t sum = 0;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          const int bq = base + 8 * lane + k;
+          const int32_t l = bq < p.batch ? __ldg(p.lengths + bq) : 0;
+          c[k] = bq < p.batch ? tc_nact(l, t_max32, tp.tout) : 0;
+          sum += c[k];
+          if (k == ew) mylen = l;
+          if (bq < p.batch && (nfo || sfe)) {
+            const int32_t f = frames_of(l, 320, 160);
+            if (nfo) nfo[bq] = f;
+            if (f == 0 && sfe) atomicOr(sfe, 1);
+          }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+        total += sum;
+      }
+      const long long a0 = (total * blockIdx.x) / gridDim.x, a1r = (total * (blockIdx.x + 1)) / gridDim.x;
+      const long long a1 = a1r - a0 > kTcListTiles ? a0 + kTcListTiles : a1r;  // (the host keeps ranges within the list)
+      if (ew == 0 && lane == 0) ctl->n_tiles = static_cast<int32_t>(a1 - a0);
+      long long acc = 0;
+      for (int base = 0; base < p.batch; base += 256) {
+        if (p.batch > 256) {  // more than one chunk: the counts of this one again (L1 / L2 hits)
+#pragma unroll
+          for (int k = 0; k < 8; ++k) {
+            const int bq = base + 8 * lane + k;
+            const int32_t l = bq < p.batch ? __ldg(p.lengths + bq) : 0;
+            c[k] = bq < p.batch ? tc_nact(l, t_max32, tp.tout) : 0;
+            if (k == ew) mylen = l;
+          }
+        }
+        int32_t sum = 0, before = 0, mine = 0;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          if (k < ew) before += c[k];
+          if (k == ew) mine = c[k];
+          sum += c[k];
+        }
+        int32_t incl = sum;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+          const int32_t v = __shfl_up_sync(0xffffffffu, incl, o);
+          if (lane >= o) incl += v;
+        }
+        const long long first = acc + (incl - sum) + before;  // active-tile index of my utterance's tile 0
+        acc += __shfl_sync(0xffffffffu, incl, 31);
+        const int bq = base + 8 * lane + ew;
+        long long jl = a0 - first, jh = a1 - first;
+        if (jl < 0) jl = 0;
+        if (jh > mine) jh = mine;
+        if (jl < jh) {
+          const int bbv = static_cast<int>(fetch_blk(bq));
+          for (int j = static_cast<int>(jl); j < static_cast<int>(jh); ++j)
+            sList[first + j - a0] = make_int4(bq, j, mylen, bbv);
+        }
+      }
+      __syncwarp();
+      if (lane == 0) tc::mbar_arrive(&ctl->list_full);
+    }
+    if (!tc::mbar_wait(&ctl->list_full, 0)) timed_out = true;
+    const int n_tiles = ctl->n_tiles;
     if (n_masks > 0 && !p.mask_table) {
       TcDrawArgs da;
-      da.lengths = p.lengths;
       da.status = p.status;
       da.seed = p.seed;
       da.first_utt = p.first_utt;
@@ -505,31 +661,22 @@ __global__ void __launch_bounds__(kTcThreads, 1)
       da.sa_F = p.sa_F;
       da.sa_T = p.sa_T;
       da.sa_p = p.sa_p;
-      da.tiles_per_utt = tp.tiles_per_utt;
-      da.total_tiles = tp.total_tiles;
-      tc_draw_tables(sMask, da, etid);
+      tc_draw_tables(sMask, da, sList, n_tiles, etid);
     }
-    int ti = 0;  // ordinal of the tile among this CTA's tiles (indexes the drawn tables)
-    TcTileIter it;
-    it.init(blockIdx.x, tp.tiles_per_utt);
-    int32_t len_nxt = __ldg(p.lengths + it.b);
-    for (int tile = blockIdx.x; tile < tp.total_tiles; tile += gridDim.x) {
-      const int b = it.b, j = it.j;
-      const int32_t len = len_nxt;  // fetched one tile ahead
-      it.step(step_b, step_j, tp.tiles_per_utt);
-      if (tile + gridDim.x < tp.total_tiles) len_nxt = __ldg(p.lengths + it.b);
+    for (int ti = 0; ti < n_tiles; ++ti) {
+      const int4 cur = sList[ti];
+      const int b = cur.x, j = cur.y;
+      const int32_t len = cur.z;
       // SpecAugment: lane i of every group-B warp fetches entry i of the utterance's mask table now
       // (at most 16 masks on this path); it is consumed after the whole tile has been reduced
       int32_t mask_entry = 0;
       if (n_masks > 0 && group == 1 && lane < 2 * n_masks)
         mask_entry = p.mask_table ? __ldg(p.mask_table + static_cast<size_t>(b) * 2 * n_masks + lane)
                                   : sMask[ti * kTcMaskEntries + lane];
-      ++ti;
       const int n_fr = frames_of(len, 320, 160);
       const int t_first = j * tp.tout;  // first OUTPUT frame of this tile; row i holds frame t_first - halo + i
-      const bool active = t_first < n_fr;
+      constexpr bool active = true;  // (the range holds active tiles only)
       const int t_row = t_first - tp.halo + row;
-      if (etid == 0 && j == 0 && p.n_frames) p.n_frames[b] = n_fr;
       // C == 1: the staged rows are free once the pair's previous TMA store has read them.  Nobody
       // writes them before the group's last chunk (all finishing work is emitted there), so the
       // hand-shake - B waits for that read and tells A - happens there, long after the read is done.
@@ -699,6 +846,21 @@ __global__ void __launch_bounds__(kTcThreads, 1)
       }
     }
     if (C == 1 && issuer) tc::bulk_wait_all();
+  }
+
+  // ---- the rows behind every utterance's last active tile: +0.0 like padded_batch
+  //      (run/train.py:192-197).  32-row blocks, split evenly over the producer and issuer warps of
+  //      the grid: they are done about one tile before the epilogue, which is left alone. ----
+  if (warp < 8) {
+    tc_walk_begin<true>(swk, p.lengths, p.batch, t_max32, tp.tout, blockIdx.x * 8u + static_cast<uint32_t>(warp),
+                        gridDim.x * 8u, lane, nullptr, nullptr);
+    TcWalk z = *swk;
+    for (; z.left > 0; tc_walk_step<true>(z, p.lengths, p.batch, t_max32, tp.tout)) {
+      const int32_t r0 = tc_nact(z.len, t_max32, tp.tout) * tp.tout + 32 * z.j;
+      const int32_t rows = t_max32 - r0 < 32 ? t_max32 - r0 : 32;
+      float4* dst = reinterpret_cast<float4*>(p.out + (static_cast<int64_t>(z.b) * p.t_max + r0) * (80 * C));
+      for (int q = lane; q < rows * 20 * C; q += 32) dst[q] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    }
   }
 
   if (timed_out && p.status) atomicOr(p.status, 0x100);
