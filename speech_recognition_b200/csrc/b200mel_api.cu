@@ -349,9 +349,13 @@ int b200mel_forward(b200mel_handle* h, const void* pcm, int32_t pcm_dtype, const
     return fail(B200MEL_ERR_INVALID_ARGUMENT, "the tensor-core kernel needs a 16-byte aligned output buffer");
   if (kernel == B200MEL_KERNEL_TC && kp.n_masks_f + kp.n_masks_t > 16)
     return fail(B200MEL_ERR_INVALID_ARGUMENT, "the tensor-core kernel handles at most 16 SpecAugment masks per utterance");
+  // (one utterance must fit one launch of the tensor-core kernel: t_max <= ~9.5 M frames)
+  const bool tc_fits = t_max > 0 && tc_max_tiles_per_launch(h->sm_count) / ((t_max + (kp.C == 3 ? 126 : 128) - 1) / (kp.C == 3 ? 126 : 128)) >= 1;
+  if (kernel == B200MEL_KERNEL_TC && t_max > 0 && !tc_fits)
+    return fail(B200MEL_ERR_UNSUPPORTED, "t_max is too large for the tensor-core kernel (use B200MEL_KERNEL_GENERIC)");
   // (the tensor-core kernel keeps one mask-table entry per lane: at most 16 masks per utterance)
   if (h->tc_ok && kernel != B200MEL_KERNEL_GENERIC && t_max > 0 && pcm_dtype == B200MEL_PCM_I16 && tc_aligned &&
-      kp.n_masks_f + kp.n_masks_t <= 16) {
+      kp.n_masks_f + kp.n_masks_t <= 16 && tc_fits) {
     const int n_masks = kp.n_masks_f + kp.n_masks_t;
     int32_t* tmp_table = nullptr;
     if (n_masks > 0 && !mask_table && !tc_draws_in_kernel(kp, h->sm_count)) {
@@ -365,11 +369,13 @@ int b200mel_forward(b200mel_handle* h, const void* pcm, int32_t pcm_dtype, const
       kp.mask_table = tmp_table;
       h->launches.fetch_add(1);
     }
-    int rc = tc_launch(h->tc, kp, h->sm_count, st);
+    int n_launched = 0;
+    int rc = tc_launch(h->tc, kp, h->sm_count, st, &n_launched);
     if (tmp_table) cudaFreeAsync(tmp_table, st);
+    h->launches.fetch_add(n_launched);
     if (rc == 2) return fail(B200MEL_ERR_CUDA, "cuTensorMapEncodeTiled failed for the output tensor");
+    if (rc == 3) return fail(B200MEL_ERR_UNSUPPORTED, "t_max is too large for the tensor-core kernel (use B200MEL_KERNEL_GENERIC)");
     if (rc != 0) return cuda_fail(cudaGetLastError(), "tc_frontend_kernel launch");
-    h->launches.fetch_add(1);
     return B200MEL_OK;
   }
 #endif

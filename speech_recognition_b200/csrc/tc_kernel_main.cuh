@@ -891,14 +891,13 @@ inline TcEncodeTiledFn tc_encode_fn() {
 // specaug_draw_from_lengths_kernel as a pre-pass and passes the table.
 inline bool tc_draws_in_kernel(const KernelParams& kp, int sm_count) {
   const int halo = kp.C == 3 ? 2 : 0, tout = kTcTileM - halo;
-  const int64_t total = ((kp.t_max + tout - 1) / tout) * kp.batch;
+  const int64_t total = ((kp.t_max + tout - 1) / tout) * kp.batch;  // (an upper bound per launch)
   const int64_t grid = total < sm_count ? total : sm_count;
   return 2 * (kp.n_masks_f + kp.n_masks_t) <= kTcMaskEntries && grid > 0 && (total + grid - 1) / grid <= kTcMaskTiles;
 }
 
-// Host launcher.  Returns 0 on success.  With SpecAugment enabled and no kp.mask_table the kernel
-// draws the tables itself: the caller checks tc_draws_in_kernel() first.
-inline int tc_launch(const TcPlan& tc, const KernelParams& kp, int sm_count, cudaStream_t st) {
+// One launch over utterances [0, kp.batch) of kp.
+inline int tc_launch_one(const TcPlan& tc, const KernelParams& kp, int sm_count, cudaStream_t st) {
   TcParams tp;
   tp.b_image = tc.d_b;
   tp.log_eps = tc.log_eps;
@@ -938,6 +937,50 @@ inline int tc_launch(const TcPlan& tc, const KernelParams& kp, int sm_count, cud
     if (cudaLaunchKernelEx(&lc, tc_frontend_kernel<1>, kp, tp, map) != cudaSuccess) return 1;
   }
   return cudaGetLastError() == cudaSuccess ? 0 : 1;
+}
+
+// Tiles one launch may cover: every CTA keeps its tile list in shared memory (kTcListTiles entries).
+// B200MEL_TC_MAX_TILES lowers it (tests of the chunked path; read once).
+inline int64_t tc_max_tiles_per_launch(int sm_count) {
+  static const int64_t forced = [] {
+    const char* e = std::getenv("B200MEL_TC_MAX_TILES");
+    return e ? std::atoll(e) : 0LL;
+  }();
+  const int64_t cap = static_cast<int64_t>(kTcListTiles) * sm_count;
+  return forced > 0 && forced < cap ? forced : cap;
+}
+
+// Host launcher.  Returns 0 on success, 2 when the tensor map cannot be encoded, 3 when one utterance
+// alone has more tiles than a launch can cover.  A batch with more tiles than that is processed in
+// consecutive utterance ranges, one launch each (same stream, so they overlap like any two steps).
+// With SpecAugment enabled and no kp.mask_table the kernel draws the tables itself: the caller checks
+// tc_draws_in_kernel() first.
+inline int tc_launch(const TcPlan& tc, const KernelParams& kp, int sm_count, cudaStream_t st, int* n_launches) {
+  const int halo = kp.C == 3 ? 2 : 0, tout = kTcTileM - halo;
+  const int64_t tiles_per_utt = (kp.t_max + tout - 1) / tout;
+  if (n_launches) *n_launches = 0;
+  if (tiles_per_utt <= 0 || kp.batch <= 0) return 0;
+  const int64_t per_launch = tc_max_tiles_per_launch(sm_count) / tiles_per_utt;
+  if (per_launch < 1) return 3;
+  const int n_masks = kp.n_masks_f + kp.n_masks_t;
+  for (int64_t b0 = 0; b0 < kp.batch; b0 += per_launch) {
+    KernelParams sub = kp;
+    sub.batch = static_cast<int32_t>(kp.batch - b0 < per_launch ? kp.batch - b0 : per_launch);
+    sub.lengths = kp.lengths + b0;
+    if (kp.offsets) {
+      sub.offsets = kp.offsets + b0;  // (element offsets into the same buffer)
+    } else {
+      sub.pcm = static_cast<const char*>(kp.pcm) + b0 * kp.row_stride * (kp.pcm_is_f32 ? 4 : 2);
+    }
+    sub.out = kp.out + b0 * kp.t_max * kp.F * kp.C;
+    if (kp.n_frames) sub.n_frames = kp.n_frames + b0;
+    if (kp.mask_table) sub.mask_table = kp.mask_table + b0 * 2 * n_masks;
+    sub.first_utt = kp.first_utt + static_cast<uint64_t>(b0);
+    const int rc = tc_launch_one(tc, sub, sm_count, st);
+    if (rc != 0) return rc;
+    if (n_launches) ++*n_launches;
+  }
+  return 0;
 }
 
 }  // namespace b200mel

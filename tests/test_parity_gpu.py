@@ -211,6 +211,39 @@ def test_tc_mask_paths_agree_with_the_oracle_draws(fe_mod, m_F, m_T):
         assert np.all(got[i, t:] == 0.0)
 
 
+def test_tc_chunked_launches_match_a_single_launch():
+    """A batch with more tiles than one launch's per-CTA tile lists can hold is processed in utterance
+    ranges; B200MEL_TC_MAX_TILES forces that path at a small size (separate process: the limit is
+    read once)."""
+    import subprocess, sys, textwrap
+    code = textwrap.dedent("""
+        import numpy as np, torch
+        from speech_recognition_b200 import FeatureFrontend
+        cfg = dict(sample_rate=16000, frame_length=320, frame_step=160, fft_length=320, num_mel_bins=80,
+                   lower_edge_hertz=80.0, upper_edge_hertz=7600.0)
+        rng = np.random.default_rng(3)
+        lengths = rng.integers(0, 48000, size=37).astype(np.int32)
+        lengths[5] = 0
+        pcm = torch.from_numpy(rng.integers(-3000, 3000, size=(37, 48000)).astype(np.int16)).cuda()
+        sa = dict(enable=True, F=27, m_F=2, T=100, p=1.0, m_T=2)
+        for delta in (False, True):
+            fe = FeatureFrontend("log-mel-spectrogram", **cfg, use_delta_accelerate=delta, spec_augment=sa)
+            out, nf = fe(pcm, lengths=lengths, seed=43, first_utterance_id=9, kernel="tc")
+            print(delta, fe.launch_count, float(out.double().abs().sum()), int(nf.sum()))
+    """)
+    import os
+    outs = []
+    for cap in ("0", "7"):
+        env = dict(os.environ, B200MEL_TC_MAX_TILES=cap, PYTHONPATH=os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+        r = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=300)
+        assert r.returncode == 0, r.stderr
+        outs.append([l.split() for l in r.stdout.strip().splitlines()])
+    whole, chunked = outs
+    for a, b in zip(whole, chunked):
+        assert a[0] == b[0] and a[2:] == b[2:]          # identical checksums and frame counts
+        assert int(b[1]) > int(a[1])                     # ... from more launches
+
+
 def test_masks_are_sharding_invariant(fe_mod):
     """Masks are a pure function of (seed, global utterance id): any split of the batch over
     ranks gives the same result (BASELINE config 3)."""
