@@ -78,4 +78,105 @@ __global__ void delta_kernel(const float* __restrict__ in, float* __restrict__ o
   }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Second stage of the tensor-core MFCC path (make_mfcc, data.py:192-241, for the shipped kspon /
+// clovacall parameters): log-mel [B, t_max, M] (written by tc_frontend_kernel<1>) ->
+// DCT-II * rsqrt(2M), first n_mfcc coefficients (data.py:235) -> SpecAugment on the coefficients
+// (run/train.py:100-110: v = num_mfcc) -> delta / delta-delta (data.py:310-328) -> [B, t_max, n_mfcc, C],
+// padding frames +0.0.  One block = 64 frames of one utterance (+ 2 frames of halo for the deltas).
+// Register blocking: a thread owns one coefficient of 8 frames, so one 128-bit broadcast read of the
+// log-mel row feeds 4 FMAs (0.375 shared-memory reads per FMA).
+// ---------------------------------------------------------------------------------------------
+constexpr int kMfccFrames = 64, kMfccGroups = 9, kMfccMaxM = 80, kMfccMaxC = 80;
+inline size_t mfcc_post_smem_bytes(int M, int n_mfcc) {
+  return sizeof(float) * (static_cast<size_t>(8 * kMfccGroups) * M + static_cast<size_t>(M) * n_mfcc + static_cast<size_t>(8 * kMfccGroups) * n_mfcc);
+}
+__global__ void __launch_bounds__(kMfccGroups * 40)
+    mfcc_post_kernel(const float* __restrict__ lm, float* __restrict__ out, const int32_t* __restrict__ lengths,
+                     int64_t t_max, int Lw, int H, int M, int n_mfcc, int C, const float* __restrict__ dct,
+                     int n_masks_f, int n_masks_t, int sa_F, int sa_T, float sa_p,
+                     const int32_t* __restrict__ mask_table, uint64_t seed, uint64_t first_utt, int32_t* status) {
+  extern __shared__ __align__(16) float mfcc_smem[];
+  const int halo = C == 3 ? 2 : 0, rows = kMfccFrames + halo;
+  float* sx = mfcc_smem;                       // [72][M]   log-mel rows (rows >= `rows` unused, zero)
+  float* sd = sx + 8 * kMfccGroups * M;        // [M][n_mfcc]
+  float* sm = sd + M * n_mfcc;                 // [72][n_mfcc] coefficients
+  __shared__ int32_t s_table[2 * kMaxMasks];
+  const int b = blockIdx.y;
+  const int64_t t0 = static_cast<int64_t>(blockIdx.x) * kMfccFrames;
+  if (t0 >= t_max) return;
+  const int32_t n_fr_all = frames_of(lengths[b], Lw, H);
+  const int64_t n_fr = n_fr_all < t_max ? n_fr_all : t_max;
+  const int n_masks = n_masks_f + n_masks_t;
+  if (threadIdx.x == 0 && n_masks > 0) {
+    if (mask_table) {
+      for (int i = 0; i < 2 * n_masks; ++i) s_table[i] = mask_table[static_cast<size_t>(b) * 2 * n_masks + i];
+    } else {
+      const int bad = specaug_draw_table(n_fr_all, n_mfcc, sa_F, n_masks_f, sa_T, sa_p, n_masks_t, seed,
+                                         first_utt + static_cast<uint64_t>(b), s_table);
+      if (bad && blockIdx.x == 0 && status) atomicOr(status, 1);
+    }
+  }
+  for (int i = threadIdx.x; i < M * n_mfcc; i += blockDim.x) sd[i] = dct[i];
+  const float* lmb = lm + static_cast<int64_t>(b) * t_max * M;
+  for (int i = threadIdx.x; i < 8 * kMfccGroups * (M / 4); i += blockDim.x) {
+    const int r = i / (M / 4), q = i - r * (M / 4);
+    const int64_t t = t0 - halo + r;
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (r < rows && t >= 0 && t < n_fr) v = *reinterpret_cast<const float4*>(lmb + t * M + 4 * q);
+    *reinterpret_cast<float4*>(sx + r * M + 4 * q) = v;
+  }
+  __syncthreads();
+  {
+    const int cw = blockDim.x / kMfccGroups;
+    const int g = threadIdx.x / cw;
+    for (int c = threadIdx.x - g * cw; c < n_mfcc; c += cw) {
+      float acc[8];
+#pragma unroll
+      for (int r = 0; r < 8; ++r) acc[r] = 0.0f;
+      for (int m = 0; m < M; m += 4) {
+        const float d0 = sd[(m + 0) * n_mfcc + c], d1 = sd[(m + 1) * n_mfcc + c], d2 = sd[(m + 2) * n_mfcc + c],
+                    d3 = sd[(m + 3) * n_mfcc + c];
+#pragma unroll
+        for (int r = 0; r < 8; ++r) {
+          const float4 x = *reinterpret_cast<const float4*>(sx + (8 * g + r) * M + m);
+          acc[r] = fmaf(x.x, d0, acc[r]);   // same order as the generic kernel: m ascending, one FMA each
+          acc[r] = fmaf(x.y, d1, acc[r]);
+          acc[r] = fmaf(x.z, d2, acc[r]);
+          acc[r] = fmaf(x.w, d3, acc[r]);
+        }
+      }
+#pragma unroll
+      for (int r = 0; r < 8; ++r) {
+        const int row = 8 * g + r;
+        const int64_t t = t0 - halo + row;
+        float v = (t >= 0 && t < n_fr) ? acc[r] : 0.0f;
+        if (n_masks > 0 && t >= 0 && t < n_fr) v *= mask_value(s_table, n_masks_f, n_masks_t, static_cast<int>(t), c);
+        sm[row * n_mfcc + c] = v;
+      }
+    }
+  }
+  __syncthreads();
+  float* ob = out + (static_cast<int64_t>(b) * t_max + t0) * n_mfcc * C;
+  const int per_row = n_mfcc * C;
+  for (int o = threadIdx.x; o < kMfccFrames * per_row; o += blockDim.x) {
+    const int r = o / per_row, e = o - r * per_row;
+    const int c = e / C, ch = e - c * C;
+    if (t0 + r >= t_max) break;
+    const int row = r + halo;
+    float val = 0.0f;
+    if (t0 + r < n_fr) {
+      const float x0 = sm[row * n_mfcc + c];
+      if (ch == 0) {
+        val = x0;
+      } else {
+        const float x1 = sm[(row - 1) * n_mfcc + c], x2 = sm[(row - 2) * n_mfcc + c];
+        const float d0 = x0 - x1, d1 = x1 - x2;
+        val = ch == 1 ? d0 : d0 - d1;
+      }
+    }
+    ob[o] = val;
+  }
+}
+
 }  // namespace b200mel

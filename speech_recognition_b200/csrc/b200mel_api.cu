@@ -80,6 +80,7 @@ struct b200mel_handle {
   TcPlan tc;
 #endif
   bool tc_ok = false;
+  cudaMemPool_t pool = nullptr;  // MFCC on the tensor-core path: stream-ordered scratch for the log-mel stage
   std::atomic<int64_t> launches{0};
   // e2e staging (b200mel_forward_host)
   std::mutex host_mu;
@@ -199,6 +200,25 @@ int b200mel_create(const b200mel_config* config, int device, b200mel_handle** ou
       h->tc_ok = false;
     }
   }
+  if (h->tc_ok && p.cfg.audio_feature_type == B200MEL_FEATURE_MFCC) {
+    // two-stage path: needs the second kernel's shared memory and a memory pool that keeps its
+    // scratch between calls (the device's default pool releases it at every synchronisation)
+    const size_t smem = mfcc_post_smem_bytes(p.cfg.num_mel_bins, p.n_mfcc_eff);
+    cudaMemPoolProps props;
+    std::memset(&props, 0, sizeof(props));
+    props.allocType = cudaMemAllocationTypePinned;
+    props.handleTypes = cudaMemHandleTypeNone;
+    props.location.type = cudaMemLocationTypeDevice;
+    props.location.id = device;
+    uint64_t keep = ~0ull;
+    if (p.cfg.num_mel_bins > kMfccMaxM || p.n_mfcc_eff > kMfccMaxC || smem > static_cast<size_t>(h->max_smem_optin) ||
+        cudaFuncSetAttribute(mfcc_post_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)) != cudaSuccess ||
+        cudaMemPoolCreate(&h->pool, &props) != cudaSuccess ||
+        cudaMemPoolSetAttribute(h->pool, cudaMemPoolAttrReleaseThreshold, &keep) != cudaSuccess) {
+      cudaGetLastError();
+      h->tc_ok = false;
+    }
+  }
 #endif
   *out_handle = h;
   return B200MEL_OK;
@@ -222,6 +242,7 @@ int b200mel_destroy(b200mel_handle* h) {
 #ifdef B200MEL_WITH_TC
   tc_plan_free(h->tc);
 #endif
+  if (h->pool) cudaMemPoolDestroy(h->pool);
   for (auto& s : h->streams)
     if (s) cudaStreamDestroy(s);
   if (h->ev_init)
@@ -358,7 +379,8 @@ int b200mel_forward(b200mel_handle* h, const void* pcm, int32_t pcm_dtype, const
       kp.n_masks_f + kp.n_masks_t <= 16 && tc_fits) {
     const int n_masks = kp.n_masks_f + kp.n_masks_t;
     int32_t* tmp_table = nullptr;
-    if (n_masks > 0 && !mask_table && !tc_draws_in_kernel(kp, h->sm_count)) {
+    if (n_masks > 0 && !mask_table && h->plan.cfg.audio_feature_type != B200MEL_FEATURE_MFCC &&
+        !tc_draws_in_kernel(kp, h->sm_count)) {
       // pre-pass: the utterances' mask tables (same Philox stream as b200mel_specaug_draw), in a
       // stream-ordered scratch buffer so that concurrent callers of one handle do not share state
       CU_CHECK(cudaMallocAsync(reinterpret_cast<void**>(&tmp_table),
@@ -369,10 +391,40 @@ int b200mel_forward(b200mel_handle* h, const void* pcm, int32_t pcm_dtype, const
       kp.mask_table = tmp_table;
       h->launches.fetch_add(1);
     }
+    // MFCC: the log-mel stage (C = 1, no masks) goes to a scratch buffer, the second kernel does the
+    // DCT, the masks on the coefficients and the deltas
+    const bool two_stage = h->plan.cfg.audio_feature_type == B200MEL_FEATURE_MFCC;
+    float* lm = nullptr;
+    KernelParams kp1 = kp;
+    if (two_stage) {
+      if (tmp_table) {  // (not reached: the pre-pass is only taken with masks, which stage 1 does not apply)
+        cudaFreeAsync(tmp_table, st);
+        tmp_table = nullptr;
+      }
+      CU_CHECK(cudaMallocFromPoolAsync(reinterpret_cast<void**>(&lm), static_cast<size_t>(batch) * t_max * kp.M * sizeof(float),
+                                       h->pool, st));
+      kp1.feature_type = B200MEL_FEATURE_LOG_MEL;
+      kp1.F = kp.M;
+      kp1.C = 1;
+      kp1.n_masks_f = kp1.n_masks_t = 0;
+      kp1.mask_table = nullptr;
+      kp1.out = lm;
+    }
     int n_launched = 0;
-    int rc = tc_launch(h->tc, kp, h->sm_count, st, &n_launched);
+    int rc = tc_launch(h->tc, kp1, h->sm_count, st, &n_launched);
     if (tmp_table) cudaFreeAsync(tmp_table, st);
     h->launches.fetch_add(n_launched);
+    if (two_stage) {
+      if (rc == 0) {
+        dim3 grid(static_cast<unsigned>((t_max + kMfccFrames - 1) / kMfccFrames), static_cast<unsigned>(batch));
+        mfcc_post_kernel<<<grid, kMfccGroups * 40, mfcc_post_smem_bytes(kp.M, kp.n_mfcc), st>>>(
+            lm, out, lengths, t_max, kp.Lw, kp.H, kp.M, kp.n_mfcc, kp.C, kp.dct, kp.n_masks_f, kp.n_masks_t, kp.sa_F,
+            kp.sa_T, kp.sa_p, mask_table, seed, first_utterance_id, status);
+        if (cudaGetLastError() != cudaSuccess) rc = 1;
+        h->launches.fetch_add(1);
+      }
+      cudaFreeAsync(lm, st);
+    }
     if (rc == 2) return fail(B200MEL_ERR_CUDA, "cuTensorMapEncodeTiled failed for the output tensor");
     if (rc == 3) return fail(B200MEL_ERR_UNSUPPORTED, "t_max is too large for the tensor-core kernel (use B200MEL_KERNEL_GENERIC)");
     if (rc != 0) return cuda_fail(cudaGetLastError(), "tc_frontend_kernel launch");

@@ -73,7 +73,8 @@ struct TcPlan {
 // Host: does this plan equal the parameter set the epilogue was generated for?
 inline bool tc_plan_matches(const HostPlan& p) {
   const b200mel_config& c = p.cfg;
-  if (c.audio_feature_type != B200MEL_FEATURE_LOG_MEL) return false;
+  // (MFCC: the log-mel stage on the tensor cores, DCT + masks + deltas in mfcc_post_kernel)
+  if (c.audio_feature_type != B200MEL_FEATURE_LOG_MEL && c.audio_feature_type != B200MEL_FEATURE_MFCC) return false;
   if (c.frame_length != 320 || c.frame_step != 160 || p.N != 320 || c.num_mel_bins != TC_MEL_BINS) return false;
   if (static_cast<int>(p.mel_w.size()) != TC_MEL_NNZ) return false;
   for (int m = 0; m < TC_MEL_BINS; ++m)

@@ -244,6 +244,32 @@ def test_tc_chunked_launches_match_a_single_launch():
         assert int(b[1]) > int(a[1])                     # ... from more launches
 
 
+def test_mfcc_two_stage_path_matches_generic_kernel(fe_mod):
+    """kspon / clovacall parameters (mfcc-40 + SpecAugment on the coefficients + delta): the
+    tensor-core log-mel stage followed by the DCT / mask / delta kernel must agree with the generic
+    kernel - identical mask zero-set and padding, values within the MFCC tolerance - ragged lengths
+    and an injected mask table included."""
+    sa = dict(enable=True, W=None, F=15, m_F=2, T=40, p=1.0, m_T=2)
+    cfg = dict(LIBRI, num_mfcc=40)
+    lengths = [48000, 31000, 16500, 20000, 100, 320]
+    batch = np.zeros((len(lengths), 48000), np.int16)
+    for i, n in enumerate(lengths):
+        batch[i, :n] = noise_int16(n, 80 + i)
+    fe = fe_mod.FeatureFrontend("mfcc", **cfg, use_delta_accelerate=True, spec_augment=sa)
+    assert fe.tc_supported
+    tol = 1e-3 * np.sqrt(160.0)
+    for kwargs in (dict(seed=11, first_utterance_id=500),
+                   dict(mask_table=torch.tensor([[3, 4, 20, 6, 10, 7, 50, 9]] * len(lengths), dtype=torch.int32))):
+        a, nfa = fe(dev(batch), lengths=lengths, kernel="tc", **kwargs)
+        g, nfg = fe(dev(batch), lengths=lengths, kernel="generic", **kwargs)
+        a, g = a.cpu().numpy(), g.cpu().numpy()
+        assert a.shape == g.shape == (6, 299, 40, 3) and torch.equal(nfa, nfg)
+        assert np.array_equal(a[..., 0] == 0, g[..., 0] == 0)          # masks and padding
+        assert np.abs(a[..., 0] - g[..., 0]).max() <= tol and np.abs(a - g).max() <= 4 * tol
+        for i, n in enumerate(nfa.cpu().numpy()):
+            assert np.all(a[i, n:] == 0.0) and not np.any(np.signbit(a[i, n:]))
+
+
 def test_masks_are_sharding_invariant(fe_mod):
     """Masks are a pure function of (seed, global utterance id): any split of the batch over
     ranks gives the same result (BASELINE config 3)."""
