@@ -84,23 +84,25 @@ __global__ void delta_kernel(const float* __restrict__ in, float* __restrict__ o
 // DCT-II * rsqrt(2M), first n_mfcc coefficients (data.py:235) -> SpecAugment on the coefficients
 // (run/train.py:100-110: v = num_mfcc) -> delta / delta-delta (data.py:310-328) -> [B, t_max, n_mfcc, C],
 // padding frames +0.0.  One block = 64 frames of one utterance (+ 2 frames of halo for the deltas).
-// Register blocking: a thread owns one coefficient of 8 frames, so one 128-bit broadcast read of the
-// log-mel row feeds 4 FMAs (0.375 shared-memory reads per FMA).
+// Register blocking: a thread owns 4 coefficients (c, c + Q, c + 2Q, c + 3Q; Q = ceil(n_mfcc / 4)) of 4
+// frames: one 128-bit read of a log-mel row feeds 16 FMAs (a 128-bit shared-memory read by a warp
+// costs four wavefronts even when it is a broadcast, so 1 coefficient per thread was LSU-bound at
+// 1.1 wavefronts per FMA instruction; this is 0.5 with all six warps of the block at work).
 // ---------------------------------------------------------------------------------------------
-constexpr int kMfccFrames = 64, kMfccGroups = 9, kMfccMaxM = 80, kMfccMaxC = 80;
+constexpr int kMfccFrames = 64, kMfccGroups = 9, kMfccMaxM = 80, kMfccMaxC = 80, kMfccThreads = 192;
 inline size_t mfcc_post_smem_bytes(int M, int n_mfcc) {
-  return sizeof(float) * (static_cast<size_t>(8 * kMfccGroups) * M + static_cast<size_t>(M) * n_mfcc + static_cast<size_t>(8 * kMfccGroups) * n_mfcc);
+  return sizeof(float) * (static_cast<size_t>(8 * kMfccGroups) * M + static_cast<size_t>(M) * n_mfcc + (n_mfcc > 40 ? 16 * 192 : 0));
 }
-__global__ void __launch_bounds__(kMfccGroups * 40)
+__global__ void __launch_bounds__(kMfccThreads)
     mfcc_post_kernel(const float* __restrict__ lm, float* __restrict__ out, const int32_t* __restrict__ lengths,
                      int64_t t_max, int Lw, int H, int M, int n_mfcc, int C, const float* __restrict__ dct,
                      int n_masks_f, int n_masks_t, int sa_F, int sa_T, float sa_p,
                      const int32_t* __restrict__ mask_table, uint64_t seed, uint64_t first_utt, int32_t* status) {
   extern __shared__ __align__(16) float mfcc_smem[];
   const int halo = C == 3 ? 2 : 0, rows = kMfccFrames + halo;
-  float* sx = mfcc_smem;                       // [72][M]   log-mel rows (rows >= `rows` unused, zero)
+  float* sx = mfcc_smem;                       // [72][M]   log-mel rows (rows >= `rows` are zero)
   float* sd = sx + 8 * kMfccGroups * M;        // [M][n_mfcc]
-  float* sm = sd + M * n_mfcc;                 // [72][n_mfcc] coefficients
+  float* sm = sx;                              // [72][n_mfcc] coefficients: reuses sx after the DCT
   __shared__ int32_t s_table[2 * kMaxMasks];
   const int b = blockIdx.y;
   const int64_t t0 = static_cast<int64_t>(blockIdx.x) * kMfccFrames;
@@ -119,63 +121,124 @@ __global__ void __launch_bounds__(kMfccGroups * 40)
   }
   for (int i = threadIdx.x; i < M * n_mfcc; i += blockDim.x) sd[i] = dct[i];
   const float* lmb = lm + static_cast<int64_t>(b) * t_max * M;
-  for (int i = threadIdx.x; i < 8 * kMfccGroups * (M / 4); i += blockDim.x) {
-    const int r = i / (M / 4), q = i - r * (M / 4);
-    const int64_t t = t0 - halo + r;
-    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (r < rows && t >= 0 && t < n_fr) v = *reinterpret_cast<const float4*>(lmb + t * M + 4 * q);
-    *reinterpret_cast<float4*>(sx + r * M + 4 * q) = v;
+  {  // 72 rows x M/4 float4, (row, quad) advanced without divisions
+    const int m4 = M >> 2, step_r = blockDim.x / m4, step_q = blockDim.x - step_r * m4;
+    int r = threadIdx.x / m4, q = threadIdx.x - r * m4;
+    while (r < 8 * kMfccGroups) {
+      const int64_t t = t0 - halo + r;
+      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (r < rows && t >= 0 && t < n_fr) v = *reinterpret_cast<const float4*>(lmb + t * M + 4 * q);
+      *reinterpret_cast<float4*>(sx + r * M + 4 * q) = v;
+      r += step_r;
+      q += step_q;
+      if (q >= m4) {
+        q -= m4;
+        ++r;
+      }
+    }
   }
   __syncthreads();
-  {
-    const int cw = blockDim.x / kMfccGroups;
-    const int g = threadIdx.x / cw;
-    for (int c = threadIdx.x - g * cw; c < n_mfcc; c += cw) {
-      float acc[8];
+  const int Q = (n_mfcc + 3) >> 2;             // coefficient quads per row group
+  const int g = threadIdx.x / Q, cq = threadIdx.x - g * Q;
+  const bool worker = g < 2 * kMfccGroups;     // 18 groups of 4 rows (Q <= 10 keeps them inside 192 threads)
+  float acc[4][4];
 #pragma unroll
-      for (int r = 0; r < 8; ++r) acc[r] = 0.0f;
+  for (int r = 0; r < 4; ++r)
+#pragma unroll
+    for (int i = 0; i < 4; ++i) acc[r][i] = 0.0f;
+  for (int pass = 0; pass < (Q > 10 ? 2 : 1); ++pass) {  // (n_mfcc > 40: the row groups in two passes)
+    const int gg = Q > 10 ? 2 * (threadIdx.x / Q) + pass : g;
+    const bool work = Q > 10 ? (threadIdx.x / Q) < kMfccGroups : worker;
+    if (work) {
+#pragma unroll
+      for (int r = 0; r < 4; ++r)
+#pragma unroll
+        for (int i = 0; i < 4; ++i) acc[r][i] = 0.0f;
+      int cc[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) cc[i] = cq + i * Q < n_mfcc ? cq + i * Q : n_mfcc - 1;  // (clamped duplicates are dropped below)
       for (int m = 0; m < M; m += 4) {
-        const float d0 = sd[(m + 0) * n_mfcc + c], d1 = sd[(m + 1) * n_mfcc + c], d2 = sd[(m + 2) * n_mfcc + c],
-                    d3 = sd[(m + 3) * n_mfcc + c];
+        float d[4][4];
 #pragma unroll
-        for (int r = 0; r < 8; ++r) {
-          const float4 x = *reinterpret_cast<const float4*>(sx + (8 * g + r) * M + m);
-          acc[r] = fmaf(x.x, d0, acc[r]);   // same order as the generic kernel: m ascending, one FMA each
-          acc[r] = fmaf(x.y, d1, acc[r]);
-          acc[r] = fmaf(x.z, d2, acc[r]);
-          acc[r] = fmaf(x.w, d3, acc[r]);
+        for (int k = 0; k < 4; ++k)
+#pragma unroll
+          for (int i = 0; i < 4; ++i) d[k][i] = sd[(m + k) * n_mfcc + cc[i]];
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+          const float4 x = *reinterpret_cast<const float4*>(sx + (4 * gg + r) * M + m);
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {  // same order as the generic kernel: m ascending, one FMA each
+            acc[r][i] = fmaf(x.x, d[0][i], acc[r][i]);
+            acc[r][i] = fmaf(x.y, d[1][i], acc[r][i]);
+            acc[r][i] = fmaf(x.z, d[2][i], acc[r][i]);
+            acc[r][i] = fmaf(x.w, d[3][i], acc[r][i]);
+          }
         }
       }
+    }
+    if (Q > 10 && pass == 0) {
+      // two-pass shape: park the first pass's coefficients in the scratch behind the DCT matrix
+      float* park = sd + M * n_mfcc;
+      if (work)
 #pragma unroll
-      for (int r = 0; r < 8; ++r) {
-        const int row = 8 * g + r;
+        for (int r = 0; r < 4; ++r)
+#pragma unroll
+          for (int i = 0; i < 4; ++i) park[(threadIdx.x * 4 + r) * 4 + i] = acc[r][i];
+    }
+  }
+  __syncthreads();  // every read of sx is done: the coefficients overwrite it
+  for (int pass = 0; pass < (Q > 10 ? 2 : 1); ++pass) {
+    const int gg = Q > 10 ? 2 * (threadIdx.x / Q) + pass : g;
+    const bool work = Q > 10 ? (threadIdx.x / Q) < kMfccGroups : worker;
+    if (work) {
+      const float* park = sd + M * n_mfcc;
+#pragma unroll
+      for (int r = 0; r < 4; ++r) {
+        const int row = 4 * gg + r;
         const int64_t t = t0 - halo + row;
-        float v = (t >= 0 && t < n_fr) ? acc[r] : 0.0f;
-        if (n_masks > 0 && t >= 0 && t < n_fr) v *= mask_value(s_table, n_masks_f, n_masks_t, static_cast<int>(t), c);
-        sm[row * n_mfcc + c] = v;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const int c = cq + i * Q;
+          if (c < n_mfcc) {
+            const float a = (Q > 10 && pass == 0) ? park[(threadIdx.x * 4 + r) * 4 + i] : acc[r][i];
+            float v = (t >= 0 && t < n_fr) ? a : 0.0f;
+            if (n_masks > 0 && t >= 0 && t < n_fr) v *= mask_value(s_table, n_masks_f, n_masks_t, static_cast<int>(t), c);
+            sm[row * n_mfcc + c] = v;
+          }
+        }
       }
     }
   }
   __syncthreads();
   float* ob = out + (static_cast<int64_t>(b) * t_max + t0) * n_mfcc * C;
+  // thread = (coefficient, quarter of the rows): consecutive rows, so x[t-1], x[t-2] slide in registers
+  // and one shared-memory read per row gives all C channels
   const int per_row = n_mfcc * C;
-  for (int o = threadIdx.x; o < kMfccFrames * per_row; o += blockDim.x) {
-    const int r = o / per_row, e = o - r * per_row;
-    const int c = e / C, ch = e - c * C;
-    if (t0 + r >= t_max) break;
-    const int row = r + halo;
-    float val = 0.0f;
-    if (t0 + r < n_fr) {
-      const float x0 = sm[row * n_mfcc + c];
-      if (ch == 0) {
-        val = x0;
-      } else {
-        const float x1 = sm[(row - 1) * n_mfcc + c], x2 = sm[(row - 2) * n_mfcc + c];
+  const int n_rows = t_max - t0 < kMfccFrames ? static_cast<int>(t_max - t0) : kMfccFrames;
+  for (int u = threadIdx.x; u < 4 * n_mfcc; u += blockDim.x) {
+    const int ph = u / n_mfcc, c = u - ph * n_mfcc;
+    const float* col = sm + halo * n_mfcc + c;
+    const int r0 = 16 * ph, r1 = r0 + 16 < n_rows ? r0 + 16 : n_rows;
+    float x1 = 0.0f, x2 = 0.0f;
+    if (C == 3) {
+      x1 = col[(r0 - 1) * n_mfcc];
+      x2 = col[(r0 - 2) * n_mfcc];
+    }
+    for (int r = r0; r < r1; ++r) {
+      const bool live = t0 + r < n_fr;
+      const float x0 = col[r * n_mfcc];
+      float* o = ob + r * per_row + c * C;
+      if (C == 3) {
         const float d0 = x0 - x1, d1 = x1 - x2;
-        val = ch == 1 ? d0 : d0 - d1;
+        o[0] = live ? x0 : 0.0f;
+        o[1] = live ? d0 : 0.0f;
+        o[2] = live ? d0 - d1 : 0.0f;
+        x2 = x1;
+        x1 = x0;
+      } else {
+        o[0] = live ? x0 : 0.0f;
       }
     }
-    ob[o] = val;
   }
 }
 

@@ -417,7 +417,7 @@ int b200mel_forward(b200mel_handle* h, const void* pcm, int32_t pcm_dtype, const
     if (two_stage) {
       if (rc == 0) {
         dim3 grid(static_cast<unsigned>((t_max + kMfccFrames - 1) / kMfccFrames), static_cast<unsigned>(batch));
-        mfcc_post_kernel<<<grid, kMfccGroups * 40, mfcc_post_smem_bytes(kp.M, kp.n_mfcc), st>>>(
+        mfcc_post_kernel<<<grid, kMfccThreads, mfcc_post_smem_bytes(kp.M, kp.n_mfcc), st>>>(
             lm, out, lengths, t_max, kp.Lw, kp.H, kp.M, kp.n_mfcc, kp.C, kp.dct, kp.n_masks_f, kp.n_masks_t, kp.sa_F,
             kp.sa_T, kp.sa_p, mask_table, seed, first_utterance_id, status);
         if (cudaGetLastError() != cudaSuccess) rc = 1;
