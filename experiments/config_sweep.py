@@ -38,19 +38,24 @@ def report(name, fe, us, audio_s, in_bytes, out_bytes, kernel, extra=None):
     print(json.dumps(row), flush=True)
 
 
-def dense_case(name, ftype, cfg, B, L, dtype=torch.int16, delta=False, sa=None, seed=0, n=30):
+def dense_case(name, ftype, cfg, B, L, dtype=torch.int16, delta=False, sa=None, seed=0, n=30, exact=False):
     fe = FeatureFrontend(ftype, **cfg, use_delta_accelerate=delta, spec_augment=sa, device=dev)
     g = torch.Generator(device="cuda").manual_seed(0)
     xs = []
     for _ in range(2):
         x = (torch.randn((B, L), device=dev, generator=g) * 0.1).clamp_(-1, 1)
-        xs.append((x * 32767).round().to(torch.int16) if dtype == torch.int16 else x)
+        if dtype == torch.int16:
+            xs.append((x * 32767).round().to(torch.int16))
+        elif exact:
+            xs.append((x * 32767).round() / 32768.0)   # what load_audio_file produces: int16 / 32768
+        else:
+            xs.append(x)
         del x
     T = fe.num_frames(L)
     outs = [torch.empty((B, T, fe.frequency_dim, fe.feature_dim), dtype=torch.float32, device=dev) for _ in range(2)]
     lens = torch.full((B,), L, dtype=torch.int32, device=dev)
     us = timed(lambda i: fe(xs[i % 2], lengths=lens, out=outs[i % 2], seed=seed, first_utterance_id=0), n=n)
-    kern = "tc" if (fe.tc_supported and dtype == torch.int16) else "generic"
+    kern = "tc" if (fe.tc_supported and (dtype == torch.int16 or exact)) else "generic"
     report(name, fe, us, B * L / cfg["sample_rate"], B * L * xs[0].element_size(),
            B * T * fe.frequency_dim * fe.feature_dim * 4, kern, {"B": B, "L": L, "T": T})
 
@@ -61,7 +66,9 @@ dense_case("config2 log-mel C=3 (delta)", "log-mel-spectrogram", LIBRI, 256, 240
 dense_case("config3 log-mel C=1 + SpecAugment", "log-mel-spectrogram", LIBRI, 256, 240000, sa=SA, seed=43)
 dense_case("config3 log-mel C=3 + SpecAugment (libri_config.yml as shipped)", "log-mel-spectrogram", LIBRI, 256, 240000,
            delta=True, sa=SA, seed=43)
-dense_case("config2 float32 PCM in, C=1", "log-mel-spectrogram", LIBRI, 256, 240000, dtype=torch.float32, n=10)
+dense_case("config2 float32 PCM in (int16 / 32768, as load_audio_file gives), C=1", "log-mel-spectrogram", LIBRI, 256, 240000,
+           dtype=torch.float32, n=10, exact=True)
+dense_case("config2 float32 PCM in (arbitrary floats), C=1", "log-mel-spectrogram", LIBRI, 256, 240000, dtype=torch.float32, n=10)
 # ---- config 4 (i): kspon / clovacall MFCC-40 + delta -------------------------------------------
 dense_case("config4 kspon mfcc-40 C=3", "mfcc", dict(LIBRI, num_mfcc=40), 256, 240000, delta=True, n=10)
 # ---- config 4 (ii): the reference's own parameter grid (tests/test_data.py:84-87) + 400/160/512 ----

@@ -97,8 +97,10 @@ __global__ void __launch_bounds__(kMfccThreads)
     mfcc_post_kernel(const float* __restrict__ lm, float* __restrict__ out, const int32_t* __restrict__ lengths,
                      int64_t t_max, int Lw, int H, int M, int n_mfcc, int C, const float* __restrict__ dct,
                      int n_masks_f, int n_masks_t, int sa_F, int sa_T, float sa_p,
-                     const int32_t* __restrict__ mask_table, uint64_t seed, uint64_t first_utt, int32_t* status) {
+                     const int32_t* __restrict__ mask_table, uint64_t seed, uint64_t first_utt, int32_t* status,
+                     const int32_t* __restrict__ gate, int gate_value) {
   extern __shared__ __align__(16) float mfcc_smem[];
+  if (gate && (*gate != 0) != (gate_value != 0)) return;  // (float32 entry: the generic kernel takes the batch)
   const int halo = C == 3 ? 2 : 0, rows = kMfccFrames + halo;
   float* sx = mfcc_smem;                       // [72][M]   log-mel rows (rows >= `rows` are zero)
   float* sd = sx + 8 * kMfccGroups * M;        // [M][n_mfcc]
@@ -240,6 +242,46 @@ __global__ void __launch_bounds__(kMfccThreads)
       }
     }
   }
+}
+
+// ---------------------------------------------------------------------------------------------
+// float32 PCM entry of the tensor-core path.  The reference's audio is int16 / 32768 in float32
+// (load_audio_file, data.py:98-99, 104-105, 116): such samples convert back to int16 exactly and the
+// tensor-core kernel (whose operand split is exact for 16-bit samples) can take them.  Dense [B,
+// row_stride] input; only samples below lengths[b] are looked at.  *flag is set when a sample is not
+// an exact int16 / 32768: the tensor-core launch then does nothing and the generic kernel runs.
+// ---------------------------------------------------------------------------------------------
+__global__ void pcm_f32_to_i16_kernel(const float* __restrict__ in, const int32_t* __restrict__ lengths, int64_t row_stride,
+                                      int16_t* __restrict__ out, int32_t* flag) {
+  const int b = blockIdx.y;
+  const int64_t len = lengths[b];
+  const float* x = in + static_cast<int64_t>(b) * row_stride;
+  int16_t* y = out + static_cast<int64_t>(b) * row_stride;
+  bool bad = false;
+  const bool vec = (row_stride & 7) == 0 && (reinterpret_cast<uintptr_t>(in) & 31) == 0;
+  const int64_t n8 = vec ? len >> 3 : 0;
+  for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n8;
+       i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+    if (*reinterpret_cast<volatile int32_t*>(flag) != 0) return;  // already decided: stop converting
+    const float4 a = __ldg(reinterpret_cast<const float4*>(x) + 2 * i), c = __ldg(reinterpret_cast<const float4*>(x) + 2 * i + 1);
+    const float v[8] = {a.x, a.y, a.z, a.w, c.x, c.y, c.z, c.w};
+    uint32_t w[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const float s0 = v[2 * k] * 32768.0f, s1 = v[2 * k + 1] * 32768.0f;
+      const float r0 = rintf(s0), r1 = rintf(s1);
+      bad = bad || !(r0 == s0 && r1 == s1 && fabsf(s0) <= 32768.0f && fabsf(s1) <= 32768.0f && s0 != 32768.0f && s1 != 32768.0f);
+      w[k] = (static_cast<uint32_t>(static_cast<int32_t>(r0)) & 0xffffu) | (static_cast<uint32_t>(static_cast<int32_t>(r1)) << 16);
+    }
+    *reinterpret_cast<uint4*>(y + 8 * i) = make_uint4(w[0], w[1], w[2], w[3]);
+  }
+  for (int64_t i = 8 * n8 + static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < len;
+       i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+    const float s0 = __ldg(x + i) * 32768.0f, r0 = rintf(s0);
+    bad = bad || !(r0 == s0 && fabsf(s0) <= 32768.0f && s0 != 32768.0f);
+    y[i] = static_cast<int16_t>(static_cast<int32_t>(r0));
+  }
+  if (__any_sync(0xffffffffu, bad) && (threadIdx.x & 31) == 0) atomicOr(flag, 1);
 }
 
 }  // namespace b200mel

@@ -1,6 +1,7 @@
 // libb200mel.so - C ABI (include/b200mel.h) over the sm_100a kernels.  No CPU fallback.
 #include <atomic>
 #include <cstdio>
+#include <algorithm>
 #include <cstdlib>
 #include <cstring>
 #include <mutex>
@@ -200,10 +201,9 @@ int b200mel_create(const b200mel_config* config, int device, b200mel_handle** ou
       h->tc_ok = false;
     }
   }
-  if (h->tc_ok && p.cfg.audio_feature_type == B200MEL_FEATURE_MFCC) {
-    // two-stage path: needs the second kernel's shared memory and a memory pool that keeps its
-    // scratch between calls (the device's default pool releases it at every synchronisation)
-    const size_t smem = mfcc_post_smem_bytes(p.cfg.num_mel_bins, p.n_mfcc_eff);
+  if (h->tc_ok) {
+    // scratch of the two-stage paths (MFCC: the log-mel stage; float32 PCM: the int16 copy) comes from a
+    // pool that keeps it between calls (the device's default pool releases at every synchronisation)
     cudaMemPoolProps props;
     std::memset(&props, 0, sizeof(props));
     props.allocType = cudaMemAllocationTypePinned;
@@ -211,10 +211,16 @@ int b200mel_create(const b200mel_config* config, int device, b200mel_handle** ou
     props.location.type = cudaMemLocationTypeDevice;
     props.location.id = device;
     uint64_t keep = ~0ull;
-    if (p.cfg.num_mel_bins > kMfccMaxM || p.n_mfcc_eff > kMfccMaxC || smem > static_cast<size_t>(h->max_smem_optin) ||
-        cudaFuncSetAttribute(mfcc_post_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)) != cudaSuccess ||
-        cudaMemPoolCreate(&h->pool, &props) != cudaSuccess ||
+    if (cudaMemPoolCreate(&h->pool, &props) != cudaSuccess ||
         cudaMemPoolSetAttribute(h->pool, cudaMemPoolAttrReleaseThreshold, &keep) != cudaSuccess) {
+      cudaGetLastError();
+      h->tc_ok = false;
+    }
+  }
+  if (h->tc_ok && p.cfg.audio_feature_type == B200MEL_FEATURE_MFCC) {
+    const size_t smem = mfcc_post_smem_bytes(p.cfg.num_mel_bins, p.n_mfcc_eff);
+    if (p.cfg.num_mel_bins > kMfccMaxM || p.n_mfcc_eff > kMfccMaxC || smem > static_cast<size_t>(h->max_smem_optin) ||
+        cudaFuncSetAttribute(mfcc_post_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)) != cudaSuccess) {
       cudaGetLastError();
       h->tc_ok = false;
     }
@@ -319,6 +325,8 @@ static void fill_params(const b200mel_handle* h, KernelParams& kp) {
   kp.halo = h->g_halo;
   kp.warps = h->g_warps;
   kp.smem_per_warp_floats = h->g_per_warp_floats;
+  kp.gate = nullptr;
+  kp.gate_value = 0;
 }
 
 int b200mel_forward(b200mel_handle* h, const void* pcm, int32_t pcm_dtype, const int64_t* offsets,
@@ -374,8 +382,29 @@ int b200mel_forward(b200mel_handle* h, const void* pcm, int32_t pcm_dtype, const
   const bool tc_fits = t_max > 0 && tc_max_tiles_per_launch(h->sm_count) / ((t_max + (kp.C == 3 ? 126 : 128) - 1) / (kp.C == 3 ? 126 : 128)) >= 1;
   if (kernel == B200MEL_KERNEL_TC && t_max > 0 && !tc_fits)
     return fail(B200MEL_ERR_UNSUPPORTED, "t_max is too large for the tensor-core kernel (use B200MEL_KERNEL_GENERIC)");
+  // float32 PCM, dense rows, kernel = auto: convert to int16 when that is exact (the reference's audio
+  // is int16 / 32768, data.py:98-116) and gate the two kernels on the outcome - no host round trip
+  void* f32_scratch = nullptr;
+  const KernelParams kp_f32 = kp;
+  const bool f32_gated = h->tc_ok && kernel == B200MEL_KERNEL_AUTO && t_max > 0 && pcm_dtype == B200MEL_PCM_F32 && !offsets &&
+                         tc_aligned && kp.n_masks_f + kp.n_masks_t <= 16 && tc_fits && row_stride > 0;
+  if (f32_gated) {
+    const size_t n = static_cast<size_t>(batch) * static_cast<size_t>(row_stride);
+    CU_CHECK(cudaMallocFromPoolAsync(&f32_scratch, 64 + n * sizeof(int16_t), h->pool, st));
+    int32_t* flag = static_cast<int32_t*>(f32_scratch);
+    int16_t* pcm16 = reinterpret_cast<int16_t*>(static_cast<char*>(f32_scratch) + 64);
+    CU_CHECK(cudaMemsetAsync(flag, 0, sizeof(int32_t), st));
+    const int64_t per_row_threads = (row_stride + 7) / 8;
+    dim3 cgrid(static_cast<unsigned>(std::min<int64_t>(64, (per_row_threads + 255) / 256)), static_cast<unsigned>(batch));
+    pcm_f32_to_i16_kernel<<<cgrid, 256, 0, st>>>(static_cast<const float*>(pcm), lengths, row_stride, pcm16, flag);
+    h->launches.fetch_add(1);
+    kp.pcm = pcm16;
+    kp.pcm_is_f32 = 0;
+    kp.gate = flag;
+    kp.gate_value = 0;
+  }
   // (the tensor-core kernel keeps one mask-table entry per lane: at most 16 masks per utterance)
-  if (h->tc_ok && kernel != B200MEL_KERNEL_GENERIC && t_max > 0 && pcm_dtype == B200MEL_PCM_I16 && tc_aligned &&
+  if (h->tc_ok && kernel != B200MEL_KERNEL_GENERIC && t_max > 0 && (pcm_dtype == B200MEL_PCM_I16 || f32_gated) && tc_aligned &&
       kp.n_masks_f + kp.n_masks_t <= 16 && tc_fits) {
     const int n_masks = kp.n_masks_f + kp.n_masks_t;
     int32_t* tmp_table = nullptr;
@@ -419,7 +448,7 @@ int b200mel_forward(b200mel_handle* h, const void* pcm, int32_t pcm_dtype, const
         dim3 grid(static_cast<unsigned>((t_max + kMfccFrames - 1) / kMfccFrames), static_cast<unsigned>(batch));
         mfcc_post_kernel<<<grid, kMfccThreads, mfcc_post_smem_bytes(kp.M, kp.n_mfcc), st>>>(
             lm, out, lengths, t_max, kp.Lw, kp.H, kp.M, kp.n_mfcc, kp.C, kp.dct, kp.n_masks_f, kp.n_masks_t, kp.sa_F,
-            kp.sa_T, kp.sa_p, mask_table, seed, first_utterance_id, status);
+            kp.sa_T, kp.sa_p, mask_table, seed, first_utterance_id, status, kp.gate, kp.gate_value);
         if (cudaGetLastError() != cudaSuccess) rc = 1;
         h->launches.fetch_add(1);
       }
@@ -428,7 +457,11 @@ int b200mel_forward(b200mel_handle* h, const void* pcm, int32_t pcm_dtype, const
     if (rc == 2) return fail(B200MEL_ERR_CUDA, "cuTensorMapEncodeTiled failed for the output tensor");
     if (rc == 3) return fail(B200MEL_ERR_UNSUPPORTED, "t_max is too large for the tensor-core kernel (use B200MEL_KERNEL_GENERIC)");
     if (rc != 0) return cuda_fail(cudaGetLastError(), "tc_frontend_kernel launch");
-    return B200MEL_OK;
+    if (!f32_gated) return B200MEL_OK;
+    // the other half of the pair: the generic kernel on the original float32 samples, if any was inexact
+    kp = kp_f32;
+    kp.gate = static_cast<const int32_t*>(f32_scratch);
+    kp.gate_value = 1;
   }
 #endif
   int64_t tiles = (t_max + h->g_ft - 1) / h->g_ft;
@@ -436,6 +469,9 @@ int b200mel_forward(b200mel_handle* h, const void* pcm, int32_t pcm_dtype, const
   dim3 grid(static_cast<unsigned>(tiles), static_cast<unsigned>(batch));
   generic_frontend_kernel<<<grid, h->g_warps * 32, h->g_smem, st>>>(kp);
   cudaError_t e = cudaGetLastError();
+#ifdef B200MEL_WITH_TC
+  if (f32_scratch) cudaFreeAsync(f32_scratch, st);  // (stream-ordered: after both kernels of the pair)
+#endif
   if (e != cudaSuccess) return cuda_fail(e, "generic_frontend_kernel launch");
   h->launches.fetch_add(1);
   return B200MEL_OK;

@@ -48,6 +48,10 @@ struct KernelParams {
   // tiling (generic kernel)
   int32_t frames_per_tile, halo, warps;
   int32_t smem_per_warp_floats;  // FFT ping-pong + scratch, in floats
+  // float32 PCM on the tensor-core path: both kernels are launched, each runs only when the device flag
+  // `*gate` (0 = every sample was an exact int16 / 32768) equals its gate_value; null = always run
+  const int32_t* gate;
+  int32_t gate_value;
 };
 
 // ---------------------------------------------------------------------------------------------

@@ -123,6 +123,7 @@ __device__ __forceinline__ float load_sample(const void* pcm, int is_f32, int64_
 __global__ void __launch_bounds__(256) generic_frontend_kernel(const KernelParams p) {
   extern __shared__ __align__(16) float smem[];
   __shared__ int32_t s_table[2 * kMaxMasks];
+  if (p.gate && (*p.gate != 0) != (p.gate_value != 0)) return;  // (the other kernel of the pair runs)
 
   const int b = blockIdx.y;
   const int tile = blockIdx.x;

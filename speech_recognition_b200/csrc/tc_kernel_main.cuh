@@ -367,6 +367,9 @@ __global__ void __launch_bounds__(kTcThreads, 1)
   if (tid == 0) { TC_STAMP(1, 31, 1) }
   tc::pdl_wait();
   if (tid == 0) { TC_STAMP(1, 31, 2) }
+  // float32 entry: when the conversion kernel found a sample that is not an exact int16, this launch
+  // does nothing (an empty batch) and the generic kernel, launched behind it, takes the batch
+  const int32_t batch_eff = (p.gate && (*p.gate != 0) != (p.gate_value != 0)) ? 0 : p.batch;
 
   if (warp >= 1 && warp < 8) {
     // ======================= PRODUCERS (warps 1-7: 224 threads) =================================
@@ -588,16 +591,16 @@ __global__ void __launch_bounds__(kTcThreads, 1)
       int32_t* sfe = (reporter && p.n_masks_t > 0) ? p.status : nullptr;
       long long total = 0;
       int32_t c[8], mylen = 0;
-      for (int base = 0; base < p.batch; base += 256) {
+      for (int base = 0; base < batch_eff; base += 256) {
         int32_t sum = 0;
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
           const int bq = base + 8 * lane + k;
-          const int32_t l = bq < p.batch ? __ldg(p.lengths + bq) : 0;
-          c[k] = bq < p.batch ? tc_nact(l, t_max32, tp.tout) : 0;
+          const int32_t l = bq < batch_eff ? __ldg(p.lengths + bq) : 0;
+          c[k] = bq < batch_eff ? tc_nact(l, t_max32, tp.tout) : 0;
           sum += c[k];
           if (k == ew) mylen = l;
-          if (bq < p.batch && (nfo || sfe)) {
+          if (bq < batch_eff && (nfo || sfe)) {
             const int32_t f = frames_of(l, 320, 160);
             if (nfo) nfo[bq] = f;
             if (f == 0 && sfe) atomicOr(sfe, 1);
@@ -611,13 +614,13 @@ __global__ void __launch_bounds__(kTcThreads, 1)
       const long long a1 = a1r - a0 > kTcListTiles ? a0 + kTcListTiles : a1r;  // (the host keeps ranges within the list)
       if (ew == 0 && lane == 0) ctl->n_tiles = static_cast<int32_t>(a1 - a0);
       long long acc = 0;
-      for (int base = 0; base < p.batch; base += 256) {
-        if (p.batch > 256) {  // more than one chunk: the counts of this one again (L1 / L2 hits)
+      for (int base = 0; base < batch_eff; base += 256) {
+        if (batch_eff > 256) {  // more than one chunk: the counts of this one again (L1 / L2 hits)
 #pragma unroll
           for (int k = 0; k < 8; ++k) {
             const int bq = base + 8 * lane + k;
-            const int32_t l = bq < p.batch ? __ldg(p.lengths + bq) : 0;
-            c[k] = bq < p.batch ? tc_nact(l, t_max32, tp.tout) : 0;
+            const int32_t l = bq < batch_eff ? __ldg(p.lengths + bq) : 0;
+            c[k] = bq < batch_eff ? tc_nact(l, t_max32, tp.tout) : 0;
             if (k == ew) mylen = l;
           }
         }
@@ -852,10 +855,10 @@ __global__ void __launch_bounds__(kTcThreads, 1)
   //      (run/train.py:192-197).  32-row blocks, split evenly over the producer and issuer warps of
   //      the grid: they are done about one tile before the epilogue, which is left alone. ----
   if (warp < 8) {
-    tc_walk_begin<true>(swk, p.lengths, p.batch, t_max32, tp.tout, blockIdx.x * 8u + static_cast<uint32_t>(warp),
+    tc_walk_begin<true>(swk, p.lengths, batch_eff, t_max32, tp.tout, blockIdx.x * 8u + static_cast<uint32_t>(warp),
                         gridDim.x * 8u, lane, nullptr, nullptr);
     TcWalk z = *swk;
-    for (; z.left > 0; tc_walk_step<true>(z, p.lengths, p.batch, t_max32, tp.tout)) {
+    for (; z.left > 0; tc_walk_step<true>(z, p.lengths, batch_eff, t_max32, tp.tout)) {
       const int32_t r0 = tc_nact(z.len, t_max32, tp.tout) * tp.tout + 32 * z.j;
       const int32_t rows = t_max32 - r0 < 32 ? t_max32 - r0 : 32;
       float4* dst = reinterpret_cast<float4*>(p.out + (static_cast<int64_t>(z.b) * p.t_max + r0) * (80 * C));

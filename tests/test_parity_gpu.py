@@ -89,8 +89,40 @@ def test_f32_entry_matches_int16_entry(fe_mod, kernel):
     b, _, _ = run_logmel(fe_mod, [pcm], kernel, dtype=np.float32)
     if kernel == "generic":
         assert np.array_equal(a, b)     # int16 * 2^-15 is exact, so both entries see the same floats
-    else:                               # auto: int16 takes the tensor-core kernel, float32 the generic one
-        assert np.abs(a - b).max() <= 1e-3
+    else:                               # auto: exact float32 samples take the tensor-core kernel too
+        assert np.array_equal(a, b)
+
+
+@pytest.mark.parametrize("ftype,extra", [("log-mel-spectrogram", {}), ("mfcc", {"num_mfcc": 40})])
+def test_f32_entry_is_gated_on_exactness(fe_mod, ftype, extra):
+    """float32 PCM with kernel = auto: samples that are exact int16 / 32768 (the reference's
+    load_audio_file output, data.py:98-116) take the tensor-core path and give bit-for-bit the int16
+    entry's result; as soon as one valid sample is not, the generic kernel takes the whole batch
+    (bit-for-bit the generic result).  Samples beyond lengths[b] are not looked at.  No host
+    round trip: both kernels are launched, a device flag gates them."""
+    sa = dict(enable=True, W=None, F=15, m_F=2, T=40, p=1.0, m_T=2)
+    fe = fe_mod.FeatureFrontend(ftype, **dict(LIBRI, **extra), use_delta_accelerate=True, spec_augment=sa)
+    lengths = [32000, 20000, 16123, 100]
+    i16 = np.zeros((4, 32000), np.int16)
+    for i, n in enumerate(lengths):
+        i16[i, :n] = noise_int16(n, 90 + i)
+    i16[0, 7] = -32768
+    f32 = i16.astype(np.float32) / 32768.0
+    f32[1, 20000:] = np.nan                               # garbage behind the utterance must not matter
+    kw = dict(lengths=lengths, seed=3, first_utterance_id=50)
+    want_tc, nf = fe(dev(i16), kernel="tc", **kw)
+    got, nf2 = fe(dev(f32), kernel="auto", **kw)
+    assert torch.equal(got, want_tc) and torch.equal(nf, nf2)
+    inexact = f32.copy()
+    inexact[2, 5000] += 1e-6
+    want_gen, _ = fe(dev(inexact), kernel="generic", **kw)
+    got2, nf3 = fe(dev(inexact), kernel="auto", **kw)
+    assert torch.equal(got2, want_gen) and torch.equal(nf, nf3)
+    over = f32.copy()
+    over[3, 10] = 1.0                                     # +32768 is not an int16
+    got3, _ = fe(dev(over), kernel="auto", **kw)
+    want3, _ = fe(dev(over), kernel="generic", **kw)
+    assert torch.equal(got3, want3)
 
 
 @pytest.mark.parametrize("kernel", KERNELS)
@@ -361,7 +393,9 @@ def test_per_example_wrappers_compose_like_the_reference(fe_mod):
     assert stepwise.shape == (249, 80, 3)
     fused_fe = fe_mod.FeatureFrontend("log-mel-spectrogram", **LIBRI, use_delta_accelerate=True,
                                       spec_augment=dict(enable=True, F=27, m_F=2, T=100, p=1.0, m_T=2))
-    fused, _ = fused_fe(dev(pcm[None]), seed=43, first_utterance_id=5, kernel="generic")
+    # (the per-example float32 entry holds exact int16 / 32768 samples, so it runs on the same
+    #  tensor-core kernel as the fused int16 call)
+    fused, _ = fused_fe(dev(pcm[None]), seed=43, first_utterance_id=5, kernel="auto")
     assert torch.equal(stepwise, fused[0])
     want = O.delta_accelerate(feat.cpu().numpy())
     assert np.array_equal(fe_mod.delta_accelerate(feat).cpu().numpy(), want)
