@@ -160,6 +160,50 @@ int b200mel_specaug_apply(const float* in, float* out, int32_t batch, int64_t t_
 int b200mel_delta(const float* in, float* out, const int32_t* n_frames, int32_t batch,
                   int64_t t_max, int32_t v, void* stream);
 
+/*
+ * Rows either side of the path: PCM / WAV ingest (N1), the feature cache's
+ * record framing (N2), and the batch contract of the models (N3).
+ */
+
+/* Host only.  Walk the RIFF chunks of a WAV file image and return the position of its sample data
+ * (what tfio.audio.AudioIOTensor(path, tf.int16) decodes, data.py:96-99).  format is the WAVE format
+ * tag (1 = integer PCM).  Fails with B200MEL_ERR_INVALID_ARGUMENT if the bytes are not a RIFF/WAVE image
+ * with a fmt and a data chunk (the reference raises at decode time). */
+int b200mel_wav_parse(const void* file_bytes, int64_t n_bytes, int32_t* format, int32_t* channels,
+                      int32_t* sample_rate, int32_t* bits_per_sample, int64_t* data_offset,
+                      int64_t* data_bytes);
+
+/* Device.  load_audio_file for 16-bit little-endian PCM payloads (data.py:94-117: the "wav" branch after
+ * b200mel_wav_parse, and the raw "pcm" branch incl. its zero byte appended to odd-length files): utterance
+ * b is the byte range [byte_offsets[b], byte_offsets[b] + byte_lengths[b]) of `bytes`, any alignment.
+ *   channels   device int32[B], or NULL = every payload is mono.  Multi-channel payloads are reduced with
+ *              reduce_mean over channels (data.py:116) and therefore need pcm_dtype F32.
+ *   pcm_out    device int16 (samples as stored: the front-end's native input) or float32 (= int16 / 32768),
+ *              dense [B, row_stride] (out_offsets NULL; longer payloads are cut at row_stride, the rest of
+ *              each row is zero) or ragged at element offsets out_offsets[b] (device int64[B]).
+ *   lengths_out device int32[B]: samples written per utterance - the `lengths` of b200mel_forward. */
+int b200mel_ingest_pcm16(const void* bytes, const int64_t* byte_offsets, const int64_t* byte_lengths,
+                         const int32_t* channels, int32_t batch, void* pcm_out, int32_t pcm_dtype,
+                         const int64_t* out_offsets, int64_t row_stride, int32_t* lengths_out,
+                         void* stream);
+
+/* Host only.  The masked CRC-32C of TFRecord framing (u64 length, u32 crc(length), payload,
+ * u32 crc(payload)) used by the reference's feature cache (run/make_tfrecord.py:55-56, data.py:64-79). */
+uint32_t b200mel_tfrecord_masked_crc(const void* data, int64_t n_bytes);
+
+/* Length of the models' conv-reduced padding mask for t_max frames: per layer
+ * `t = (t - (kernel - stride)) / stride` (models/las.py:209-213, models/deepspeech2.py:71-73).
+ * group_out receives the product of the strides.  Host only. */
+int b200mel_audio_mask_length(int64_t t_max, const int32_t* time_kernel_sizes, const int32_t* time_strides,
+                              int32_t n_layers, int64_t* reduced_out, int32_t* group_out);
+
+/* Device.  _audio_mask of the models (models/las.py:205-217, models/deepspeech2.py:68-78) on a padded batch
+ * feat [B, t_max, row_elems] float32 (row_elems = frequency_dim * feature_dim): frame t is real when any of
+ * its values != 0 (AUDIO_PAD_VALUE), the first reduced * group frames are OR-ed in groups of `group`.
+ * mask_out: device uint8 [B, reduced] (1 = real). */
+int b200mel_audio_mask(const float* feat, int32_t batch, int64_t t_max, int64_t row_elems, int32_t group,
+                       int64_t reduced, uint8_t* mask_out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

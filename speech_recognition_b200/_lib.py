@@ -63,6 +63,12 @@ SIGNATURES = {
                                         _vp, _vp, _vp]),
     "b200mel_specaug_apply": (_c.c_int, [_vp, _vp, _i32, _i64, _i32, _i32, _vp, _i32, _i32, _vp]),
     "b200mel_delta": (_c.c_int, [_vp, _vp, _vp, _i32, _i64, _i32, _vp]),
+    "b200mel_wav_parse": (_c.c_int, [_vp, _i64, _c.POINTER(_i32), _c.POINTER(_i32), _c.POINTER(_i32),
+                                     _c.POINTER(_i32), _c.POINTER(_i64), _c.POINTER(_i64)]),
+    "b200mel_ingest_pcm16": (_c.c_int, [_vp, _vp, _vp, _vp, _i32, _vp, _i32, _vp, _i64, _vp, _vp]),
+    "b200mel_tfrecord_masked_crc": (_c.c_uint32, [_vp, _i64]),
+    "b200mel_audio_mask_length": (_c.c_int, [_i64, _vp, _vp, _i32, _c.POINTER(_i64), _c.POINTER(_i32)]),
+    "b200mel_audio_mask": (_c.c_int, [_vp, _i32, _i64, _i64, _i32, _i64, _vp, _vp]),
 }
 
 _lock = threading.Lock()

@@ -13,6 +13,8 @@
 #include "aux_kernels.cuh"
 #include "common.cuh"
 #include "generic_kernel.cuh"
+#include "host_io.h"
+#include "ingest_kernels.cuh"
 #include "plan.h"
 #ifdef B200MEL_WITH_TC
 #include "tc_kernel.cuh"
@@ -645,6 +647,103 @@ int b200mel_delta(const float* in, float* out, const int32_t* n_frames, int32_t 
   delta_kernel<<<dim3(static_cast<unsigned>(blocks), batch), 256, 0, st>>>(in, out, n_frames, t_max, v);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return cuda_fail(e, "delta_kernel launch");
+  return B200MEL_OK;
+}
+
+int b200mel_wav_parse(const void* file_bytes, int64_t n_bytes, int32_t* format, int32_t* channels,
+                      int32_t* sample_rate, int32_t* bits_per_sample, int64_t* data_offset, int64_t* data_bytes) {
+  if (!file_bytes || n_bytes < 0) return fail(B200MEL_ERR_INVALID_ARGUMENT, "null or negative-size file image");
+  WavInfo w;
+  int rc = wav_parse(static_cast<const uint8_t*>(file_bytes), n_bytes, &w);
+  if (rc != 0) {
+    static const char* why[] = {"", "not a RIFF/WAVE image", "data chunk before fmt chunk", "no data chunk",
+                                "truncated fmt chunk"};
+    return fail(B200MEL_ERR_INVALID_ARGUMENT, std::string("wav: ") + why[rc]);
+  }
+  if (format) *format = w.format;
+  if (channels) *channels = w.channels;
+  if (sample_rate) *sample_rate = w.sample_rate;
+  if (bits_per_sample) *bits_per_sample = w.bits;
+  if (data_offset) *data_offset = w.data_offset;
+  if (data_bytes) *data_bytes = w.data_bytes;
+  return B200MEL_OK;
+}
+
+int b200mel_ingest_pcm16(const void* bytes, const int64_t* byte_offsets, const int64_t* byte_lengths,
+                         const int32_t* channels, int32_t batch, void* pcm_out, int32_t pcm_dtype,
+                         const int64_t* out_offsets, int64_t row_stride, int32_t* lengths_out, void* stream) {
+  if (batch < 0 || row_stride < 0) return fail(B200MEL_ERR_INVALID_ARGUMENT, "negative size");
+  if (pcm_dtype != B200MEL_PCM_I16 && pcm_dtype != B200MEL_PCM_F32)
+    return fail(B200MEL_ERR_INVALID_ARGUMENT, "pcm_dtype must be B200MEL_PCM_I16 or B200MEL_PCM_F32");
+  if (channels && pcm_dtype != B200MEL_PCM_F32)
+    return fail(B200MEL_ERR_INVALID_ARGUMENT,
+                "multi-channel payloads are channel means (data.py:116) and need float32 output");
+  if (batch > 65535) return fail(B200MEL_ERR_UNSUPPORTED, "batch > 65535: split the call");
+  if (batch == 0) return B200MEL_OK;
+  if (!bytes || !byte_offsets || !byte_lengths || !pcm_out || !lengths_out)
+    return fail(B200MEL_ERR_INVALID_ARGUMENT, "null buffer");
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  // 148 SMs x 8 resident blocks of 256 threads, split over the utterances
+  unsigned bx = static_cast<unsigned>(std::max(1, (1184 + batch - 1) / batch));
+  dim3 grid(bx, static_cast<unsigned>(batch));
+  const uint8_t* src = static_cast<const uint8_t*>(bytes);
+  if (channels) {
+    ingest_multi_kernel<<<grid, 256, 0, st>>>(src, byte_offsets, byte_lengths, channels,
+                                              static_cast<float*>(pcm_out), out_offsets, row_stride, lengths_out);
+  } else if (pcm_dtype == B200MEL_PCM_I16) {
+    ingest_mono_kernel<int16_t><<<grid, 256, 0, st>>>(src, byte_offsets, byte_lengths,
+                                                      static_cast<int16_t*>(pcm_out), out_offsets, row_stride,
+                                                      lengths_out);
+  } else {
+    ingest_mono_kernel<float><<<grid, 256, 0, st>>>(src, byte_offsets, byte_lengths, static_cast<float*>(pcm_out),
+                                                    out_offsets, row_stride, lengths_out);
+  }
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return cuda_fail(e, "ingest kernel launch");
+  return B200MEL_OK;
+}
+
+uint32_t b200mel_tfrecord_masked_crc(const void* data, int64_t n_bytes) {
+  if (!data || n_bytes <= 0) return tfrecord_masked_crc(nullptr, 0);
+  return tfrecord_masked_crc(static_cast<const uint8_t*>(data), n_bytes);
+}
+
+int b200mel_audio_mask_length(int64_t t_max, const int32_t* time_kernel_sizes, const int32_t* time_strides,
+                              int32_t n_layers, int64_t* reduced_out, int32_t* group_out) {
+  if (t_max < 0 || n_layers < 0 || (n_layers > 0 && (!time_kernel_sizes || !time_strides)))
+    return fail(B200MEL_ERR_INVALID_ARGUMENT, "bad audio-mask layer list");
+  int64_t t = t_max, g = 1;
+  for (int i = 0; i < n_layers; ++i) {
+    int64_t k = time_kernel_sizes[i], s = time_strides[i];
+    if (k < 1 || s < 1) return fail(B200MEL_ERR_INVALID_ARGUMENT, "kernel sizes and strides must be >= 1");
+    t -= k - s;
+    // Python floor division (models/las.py:210-213): negative lengths floor towards -inf, then clamp
+    t = t >= 0 ? t / s : -((-t + s - 1) / s);
+    g *= s;
+    if (g > (1 << 20)) return fail(B200MEL_ERR_UNSUPPORTED, "stride product too large");
+  }
+  if (t < 0) t = 0;  // a slice [:negative * g] of the frame axis: clamp (an empty mask)
+  if (reduced_out) *reduced_out = t;
+  if (group_out) *group_out = static_cast<int32_t>(g);
+  return B200MEL_OK;
+}
+
+int b200mel_audio_mask(const float* feat, int32_t batch, int64_t t_max, int64_t row_elems, int32_t group,
+                       int64_t reduced, uint8_t* mask_out, void* stream) {
+  if (batch < 0 || t_max < 0 || row_elems < 0 || group < 1 || reduced < 0)
+    return fail(B200MEL_ERR_INVALID_ARGUMENT, "negative size");
+  if (reduced * group > t_max) return fail(B200MEL_ERR_INVALID_ARGUMENT, "reduced * group exceeds t_max");
+  if (batch > 65535) return fail(B200MEL_ERR_UNSUPPORTED, "batch > 65535: split the call");
+  if (batch == 0 || reduced == 0) return B200MEL_OK;
+  if (!feat || !mask_out) return fail(B200MEL_ERR_INVALID_ARGUMENT, "null buffer");
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  int64_t want = (reduced + 7) / 8;  // 8 warps per block
+  int64_t cap = std::max<int64_t>(1, (1184 + batch - 1) / batch);
+  unsigned bx = static_cast<unsigned>(std::min(want, cap));
+  audio_mask_kernel<<<dim3(bx, static_cast<unsigned>(batch)), 256, 0, st>>>(feat, t_max, row_elems, group, reduced,
+                                                                           mask_out);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return cuda_fail(e, "audio_mask_kernel launch");
   return B200MEL_OK;
 }
 

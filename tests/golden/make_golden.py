@@ -47,6 +47,17 @@ def main():
         out["feature_%d" % i] = feat
         out["tokens_%d" % i] = tokens
     np.savez_compressed(os.path.join(HERE, "ref_wav_dataset_tfrecord.npz"), **out)
+    # data fixtures for the rows either side of the path: the reference's feature cache
+    # file itself (480 bytes; byte-identity pin of feature_cache.py) and the header of its test.wav
+    with open(os.path.join(ref, "tests", "data", "wav_dataset.tfrecord"), "rb") as f:
+        cache = f.read()
+    with open(os.path.join(HERE, "ref_wav_dataset.tfrecord"), "wb") as f:
+        f.write(cache)
+    with open(os.path.join(ref, "tests", "data", "audio_files", "test.wav"), "rb") as f:
+        wav = f.read()
+    with open(os.path.join(HERE, "ref_test_wav_header.bin"), "wb") as f:
+        f.write(wav[:44])
+    assert not any(wav[44:]) and len(wav) == 132344  # the payload is digital silence: only the header is kept
     print("records:", len(examples), "feature shape:", examples[0][0].shape,
           "unique values:", np.unique(examples[0][0]), "pcm:", pcm.shape, "rate:", rate,
           "pcm min/max:", pcm.min(), pcm.max())
