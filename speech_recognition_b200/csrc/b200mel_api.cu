@@ -197,8 +197,10 @@ int b200mel_create(const b200mel_config* config, int device, b200mel_handle** ou
   }
   if (h->tc_ok) {
     // per-device function attribute: set it while this handle's device is current
-    if (cudaFuncSetAttribute(tc_frontend_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmemTotal) != cudaSuccess ||
-        cudaFuncSetAttribute(tc_frontend_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmemTotal) != cudaSuccess) {
+    if (cudaFuncSetAttribute(tc_frontend_kernel<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmemTotal) != cudaSuccess ||
+        cudaFuncSetAttribute(tc_frontend_kernel<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmemTotal) != cudaSuccess ||
+        cudaFuncSetAttribute(tc_frontend_kernel<3, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmemTotal) != cudaSuccess ||
+        cudaFuncSetAttribute(tc_frontend_kernel<3, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmemTotal) != cudaSuccess) {
       cudaGetLastError();
       h->tc_ok = false;
     }
@@ -683,8 +685,8 @@ int b200mel_ingest_pcm16(const void* bytes, const int64_t* byte_offsets, const i
   if (!bytes || !byte_offsets || !byte_lengths || !pcm_out || !lengths_out)
     return fail(B200MEL_ERR_INVALID_ARGUMENT, "null buffer");
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-  // 148 SMs x 8 resident blocks of 256 threads, split over the utterances
-  unsigned bx = static_cast<unsigned>(std::max(1, (1184 + batch - 1) / batch));
+  // at most one resident wave (148 SMs x 8 blocks of 256 threads), split over the utterances
+  unsigned bx = static_cast<unsigned>(std::max(1, 1184 / batch));
   dim3 grid(bx, static_cast<unsigned>(batch));
   const uint8_t* src = static_cast<const uint8_t*>(bytes);
   if (channels) {
@@ -733,15 +735,13 @@ int b200mel_audio_mask(const float* feat, int32_t batch, int64_t t_max, int64_t 
   if (batch < 0 || t_max < 0 || row_elems < 0 || group < 1 || reduced < 0)
     return fail(B200MEL_ERR_INVALID_ARGUMENT, "negative size");
   if (reduced * group > t_max) return fail(B200MEL_ERR_INVALID_ARGUMENT, "reduced * group exceeds t_max");
-  if (batch > 65535) return fail(B200MEL_ERR_UNSUPPORTED, "batch > 65535: split the call");
   if (batch == 0 || reduced == 0) return B200MEL_OK;
   if (!feat || !mask_out) return fail(B200MEL_ERR_INVALID_ARGUMENT, "null buffer");
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-  int64_t want = (reduced + 7) / 8;  // 8 warps per block
-  int64_t cap = std::max<int64_t>(1, (1184 + batch - 1) / batch);
-  unsigned bx = static_cast<unsigned>(std::min(want, cap));
-  audio_mask_kernel<<<dim3(bx, static_cast<unsigned>(batch)), 256, 0, st>>>(feat, t_max, row_elems, group, reduced,
-                                                                           mask_out);
+  // one warp per entry, at most one resident wave (148 SMs x 8 blocks of 8 warps)
+  const int64_t want = (static_cast<int64_t>(batch) * reduced + 7) / 8;
+  const unsigned bx = static_cast<unsigned>(std::min<int64_t>(want, 1184));
+  audio_mask_kernel<<<bx, 256, 0, st>>>(feat, batch, t_max, row_elems, group, reduced, mask_out);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return cuda_fail(e, "audio_mask_kernel launch");
   return B200MEL_OK;

@@ -147,28 +147,37 @@ ingest_multi_kernel(const uint8_t* __restrict__ bytes, const int64_t* __restrict
 // _audio_mask (models/las.py:205-217, models/deepspeech2.py:68-78): frame t is "real" when any of its
 // F*C values differs from the pad value 0 (so -0.0 and +0.0 both count as padding, NaN as real);
 // group consecutive frames by the product of the convolution time strides and OR them.
-// One warp per output entry, 128-bit loads when the row group is 16-byte aligned.
+// One warp per output entry over a flat grid-stride loop of all B * reduced entries (one resident wave),
+// 128-bit loads when the row group is 16-byte aligned, two in flight per lane.
 __global__ void __launch_bounds__(256)
-audio_mask_kernel(const float* __restrict__ feat, int64_t t_max, int64_t row_elems, int group, int64_t reduced,
+audio_mask_kernel(const float* __restrict__ feat, int batch, int64_t t_max, int64_t row_elems, int group, int64_t reduced,
                   uint8_t* __restrict__ mask) {
-  const int b = blockIdx.y;
   const int lane = threadIdx.x & 31;
   const int64_t warps = (static_cast<int64_t>(gridDim.x) * blockDim.x) >> 5;
   const int64_t n = static_cast<int64_t>(group) * row_elems;
-  for (int64_t r = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5; r < reduced; r += warps) {
-    const float* p = feat + (static_cast<int64_t>(b) * t_max + r * group) * row_elems;
+  const int64_t total = static_cast<int64_t>(batch) * reduced;
+  for (int64_t e = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5; e < total; e += warps) {
+    const int64_t b = e / reduced, r = e - b * reduced;
+    const float* p = feat + (b * t_max + r * group) * row_elems;
     bool any = false;
     if (((reinterpret_cast<uintptr_t>(p) & 15) == 0) && (n & 3) == 0) {
       const float4* q = reinterpret_cast<const float4*>(p);
-      for (int64_t i = lane; i < (n >> 2); i += 32) {
-        float4 v = __ldg(q + i);
+      const int64_t n4 = n >> 2;
+      int64_t i = lane;
+      for (; i + 32 < n4; i += 64) {
+        const float4 v = __ldg(q + i), w = __ldg(q + i + 32);
+        any |= (v.x != 0.0f) | (v.y != 0.0f) | (v.z != 0.0f) | (v.w != 0.0f) | (w.x != 0.0f) | (w.y != 0.0f) |
+               (w.z != 0.0f) | (w.w != 0.0f);
+      }
+      if (i < n4) {
+        const float4 v = __ldg(q + i);
         any |= (v.x != 0.0f) | (v.y != 0.0f) | (v.z != 0.0f) | (v.w != 0.0f);
       }
     } else {
       for (int64_t i = lane; i < n; i += 32) any |= (__ldg(p + i) != 0.0f);
     }
-    unsigned m = __ballot_sync(0xFFFFFFFFu, any);
-    if (lane == 0) mask[static_cast<int64_t>(b) * reduced + r] = m ? 1 : 0;
+    const unsigned m = __ballot_sync(0xFFFFFFFFu, any);
+    if (lane == 0) mask[e] = m ? 1 : 0;
   }
 }
 
