@@ -5,7 +5,7 @@ sm_100a CUDA kernels behind a C ABI (include/b200mel.h, lib/libb200mel.so).
 There is no CPU implementation in this package: every entry point runs on a CUDA device and fails
 loudly if the library or a device is missing.
 """
-from . import data  # noqa: F401
+from . import batching, data, feature_cache, ingest  # noqa: F401
 from .configs import DataConfig, SpecAugmentConfig  # noqa: F401
 from .data import (  # noqa: F401
     delta_accelerate,
@@ -16,6 +16,7 @@ from .data import (  # noqa: F401
     spec_augment,
 )
 from .frontend import FeatureFrontend  # noqa: F401
+from .ingest import load_audio_file  # noqa: F401
 
 __all__ = [
     "DataConfig",
@@ -27,4 +28,8 @@ __all__ = [
     "spec_augment",
     "delta_accelerate",
     "set_random_seed",
+    "load_audio_file",
+    "ingest",
+    "batching",
+    "feature_cache",
 ]

@@ -72,7 +72,7 @@ def audio_mask(features: torch.Tensor, time_kernel_sizes: Sequence[int], time_st
     stream = torch.cuda.current_stream(features.device).cuda_stream
     _lib.check(_lib.load().b200mel_audio_mask(_ptr(features), B, T, row, group, reduced, _ptr(mask),
                                               ctypes.c_void_p(stream)))
-    return mask.bool()
+    return mask.view(torch.bool)  # 0 / 1 bytes: a view, no second kernel
 
 
 def assemble_batch(frontend, pcm, lengths, token_lengths: Optional[torch.Tensor] = None,
