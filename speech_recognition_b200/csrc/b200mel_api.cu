@@ -376,10 +376,11 @@ int b200mel_forward(b200mel_handle* h, const void* pcm, int32_t pcm_dtype, const
     if (!n_frames) return B200MEL_OK;
   }
 #ifdef B200MEL_WITH_TC
-  // the tensor-core kernel stores rows with 16-byte bulk copies / float4
-  const bool tc_aligned = (reinterpret_cast<uintptr_t>(out) & 15) == 0;
+  // the tensor-core kernel stores rows with 16-byte bulk copies (C = 1) / 256-bit stores (C = 3)
+  const bool tc_aligned = (reinterpret_cast<uintptr_t>(out) & (kp.C == 3 ? 31 : 15)) == 0;
   if (kernel == B200MEL_KERNEL_TC && !tc_aligned)
-    return fail(B200MEL_ERR_INVALID_ARGUMENT, "the tensor-core kernel needs a 16-byte aligned output buffer");
+    return fail(B200MEL_ERR_INVALID_ARGUMENT,
+                "the tensor-core kernel needs a 16-byte (with delta features: 32-byte) aligned output buffer");
   if (kernel == B200MEL_KERNEL_TC && kp.n_masks_f + kp.n_masks_t > 16)
     return fail(B200MEL_ERR_INVALID_ARGUMENT, "the tensor-core kernel handles at most 16 SpecAugment masks per utterance");
   // (one utterance must fit one launch of the tensor-core kernel: t_max <= ~9.5 M frames)

@@ -858,33 +858,69 @@ __global__ void __launch_bounds__(kTcThreads, 1)
         }
       } else {
         tc::named_bar_sync(9, 256);  // staged (and masked) rows visible to the 8 epilogue warps
-        // ---- copy-out with delta / delta-delta: staged tile -> HBM, 128-bit, fully coalesced -----
+        // ---- copy-out with delta / delta-delta: staged tile -> HBM.  A work item is a PAIR of float4
+        //      groups of one row (8 mel bins): its 24 outputs are 96 contiguous bytes = three whole 32-byte
+        //      sectors, written with three 256-bit stores (the first version wrote 48 bytes per item with
+        //      128-bit stores: every sector arrived at L2 in two halves).  128 rows x 10 pairs = exactly
+        //      five items per thread; the next item's six shared-memory loads are issued before the current
+        //      item's arithmetic and stores (a shared-memory round trip costs >100 cycles while the MMAs
+        //      stream their operands). ----
         float* out_b = p.out + static_cast<int64_t>(b) * p.t_max * 240;
-        int i = etid / 20, quad = etid - 20 * i;
-        for (int it = 0; it < 10; ++it) {
-          const int t = t_first - tp.halo + i;
-          if (i >= tp.halo && t < p.t_max) {
-            float4 x0 = make_float4(0.f, 0.f, 0.f, 0.f), x1 = x0, x2 = x0;
-            if (t < n_fr) {
-              x0 = *reinterpret_cast<const float4*>(sOut + i * kTcOutPitch + 4 * quad);
-              if (t >= 1) x1 = *reinterpret_cast<const float4*>(sOut + (i - 1) * kTcOutPitch + 4 * quad);
-              if (t >= 2) x2 = *reinterpret_cast<const float4*>(sOut + (i - 2) * kTcOutPitch + 4 * quad);
-            }
-            // (x, x - x1, (x - x1) - (x1 - x2)) per channel, interleaved [.., m, 3]
-            const float dx = x0.x - x1.x, dy = x0.y - x1.y, dz = x0.z - x1.z, dw = x0.w - x1.w;
-            const float ex = x1.x - x2.x, ey = x1.y - x2.y, ez = x1.z - x2.z, ew = x1.w - x2.w;
-            float4* o = reinterpret_cast<float4*>(out_b + (static_cast<int64_t>(t) * 80 + 4 * quad) * 3);
-            o[0] = make_float4(x0.x, dx, dx - ex, x0.y);
-            o[1] = make_float4(dy, dy - ey, x0.z, dz);
-            o[2] = make_float4(dz - ez, x0.w, dw, dw - ew);
-          }
-          quad += 16;
-          i += 12;
-          if (quad >= 20) {
-            quad -= 20;
-            i += 1;
-          }
-        }
+        float4 cx[2][6];
+        bool c_store[2];
+        float* c_dst[2];
+#define TC_CO_LOAD(S, IT)                                                                              \
+  {                                                                                                    \
+    const int item = etid + 256 * (IT);                                                                \
+    const int i = item / 10, pr = item - 10 * i;                                                       \
+    const int t = t_first - tp.halo + i;                                                               \
+    c_store[S] = i >= tp.halo && t < p.t_max;                                                          \
+    c_dst[S] = out_b + (static_cast<int64_t>(t) * 80 + 8 * pr) * 3;                                    \
+    const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);                                                 \
+    _Pragma("unroll") for (int k = 0; k < 6; ++k) cx[S][k] = z4;                                       \
+    if (c_store[S] && t < n_fr) {                                                                      \
+      const float* r0 = sOut + i * kTcOutPitch + 8 * pr;                                               \
+      cx[S][0] = *reinterpret_cast<const float4*>(r0);                                                 \
+      cx[S][1] = *reinterpret_cast<const float4*>(r0 + 4);                                             \
+      if (t >= 1) {                                                                                    \
+        cx[S][2] = *reinterpret_cast<const float4*>(r0 - kTcOutPitch);                                 \
+        cx[S][3] = *reinterpret_cast<const float4*>(r0 - kTcOutPitch + 4);                             \
+      }                                                                                                \
+      if (t >= 2) {                                                                                    \
+        cx[S][4] = *reinterpret_cast<const float4*>(r0 - 2 * kTcOutPitch);                             \
+        cx[S][5] = *reinterpret_cast<const float4*>(r0 - 2 * kTcOutPitch + 4);                         \
+      }                                                                                                \
+    }                                                                                                  \
+  }
+        // (x, x - x1, (x - x1) - (x1 - x2)) per bin, interleaved [.., m, 3]
+#define TC_CO_STORE(S)                                                                                 \
+  if (c_store[S]) {                                                                                    \
+    const float x0[8] = {cx[S][0].x, cx[S][0].y, cx[S][0].z, cx[S][0].w, cx[S][1].x, cx[S][1].y, cx[S][1].z, cx[S][1].w}; \
+    const float x1[8] = {cx[S][2].x, cx[S][2].y, cx[S][2].z, cx[S][2].w, cx[S][3].x, cx[S][3].y, cx[S][3].z, cx[S][3].w}; \
+    const float x2[8] = {cx[S][4].x, cx[S][4].y, cx[S][4].z, cx[S][4].w, cx[S][5].x, cx[S][5].y, cx[S][5].z, cx[S][5].w}; \
+    float o[24];                                                                                       \
+    _Pragma("unroll") for (int m = 0; m < 8; ++m) {                                                    \
+      const float d = x0[m] - x1[m], e = x1[m] - x2[m];                                                \
+      o[3 * m] = x0[m];                                                                                \
+      o[3 * m + 1] = d;                                                                                \
+      o[3 * m + 2] = d - e;                                                                            \
+    }                                                                                                  \
+    tc::st_global_v8(c_dst[S], o);                                                                     \
+    tc::st_global_v8(c_dst[S] + 8, o + 8);                                                             \
+    tc::st_global_v8(c_dst[S] + 16, o + 16);                                                           \
+  }
+        TC_CO_LOAD(0, 0)
+        TC_CO_LOAD(1, 1)
+        TC_CO_STORE(0)
+        TC_CO_LOAD(0, 2)
+        TC_CO_STORE(1)
+        TC_CO_LOAD(1, 3)
+        TC_CO_STORE(0)
+        TC_CO_LOAD(0, 4)
+        TC_CO_STORE(1)
+        TC_CO_STORE(0)
+#undef TC_CO_LOAD
+#undef TC_CO_STORE
         tc::named_bar_sync(9, 256);  // the staging tile may be overwritten
       }
     }
