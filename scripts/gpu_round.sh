@@ -19,4 +19,6 @@ echo "ncu launches exit $?"
 $CMD > gpurun_out/${TAG}_plain2.log 2>&1 && \
 ncu --set full --clock-control none --import-source on -k regex:${KREGEX} -s 5 -c 2 -f -o gpurun_out/${TAG}_prof $CMD > gpurun_out/${TAG}_ncu_full.log 2>&1
 echo "ncu full exit $?"
+python experiments/config_sweep.py > gpurun_out/${TAG}_configs.jsonl 2> gpurun_out/${TAG}_configs.err; echo "config sweep exit $?"
+python experiments/aux_bench.py > gpurun_out/${TAG}_aux.json 2> gpurun_out/${TAG}_aux.err; echo "aux bench exit $?"; cat gpurun_out/${TAG}_aux.json
 ls -la gpurun_out | tail -n 20
