@@ -137,6 +137,20 @@ int b200mel_forward_host(b200mel_handle* handle, const void* pcm_host, int32_t p
                          int32_t* n_frames_host, uint64_t seed, uint64_t first_utterance_id,
                          int32_t kernel);
 
+/* The same call split in two, for pipelines that keep the link busy in both directions: _submit enqueues
+ * the step (H2D chunks, kernels, D2H chunks) on staging slot 0 or 1 and returns; _wait blocks until that
+ * step's `out_host` / `n_frames_host` are complete.  Submitting step i+1 on the other slot before waiting
+ * for step i lets its uploads overlap step i's downloads - what tf.data's prefetch does for the reference
+ * (run/train.py:194).  Host buffers must stay valid (and should be pinned) until the wait returns; a
+ * submit on a slot whose previous step has not been waited for waits for it first.
+ * b200mel_forward_host == _submit(slot 0) + _wait(0). */
+int b200mel_forward_host_submit(b200mel_handle* handle, const void* pcm_host, int32_t pcm_dtype,
+                                const int64_t* offsets_host, const int32_t* lengths_host, int32_t batch,
+                                int64_t row_stride, int64_t total_samples, float* out_host,
+                                int64_t t_max, int32_t* n_frames_host, uint64_t seed,
+                                uint64_t first_utterance_id, int32_t kernel, int32_t slot);
+int b200mel_forward_host_wait(b200mel_handle* handle, int32_t slot);
+
 /*
  * Stand-alone stages, for callers that compose the reference's per-example maps one by one
  * (run/train.py:88-116) instead of using the fused call.

@@ -85,17 +85,22 @@ struct b200mel_handle {
   bool tc_ok = false;
   cudaMemPool_t pool = nullptr;  // MFCC on the tensor-core path: stream-ordered scratch for the log-mel stage
   std::atomic<int64_t> launches{0};
-  // e2e staging (b200mel_forward_host)
+  // e2e staging (b200mel_forward_host / _submit / _wait): two slots, so that the uploads of one step
+  // overlap the downloads of the previous one on the full-duplex link
   std::mutex host_mu;
-  void* s_pcm = nullptr;
-  size_t s_pcm_bytes = 0;
-  float* s_out = nullptr;
-  size_t s_out_bytes = 0;
-  int32_t* s_small = nullptr;  // lengths | n_frames | status
-  int64_t* s_offsets = nullptr;
-  size_t s_small_cap = 0;
+  struct HostSlot {
+    void* s_pcm = nullptr;
+    size_t s_pcm_bytes = 0;
+    float* s_out = nullptr;
+    size_t s_out_bytes = 0;
+    int32_t* s_small = nullptr;  // lengths | n_frames | status
+    int64_t* s_offsets = nullptr;
+    size_t s_small_cap = 0;
+    cudaEvent_t ev_in[64];
+    cudaEvent_t ev_done_k = nullptr, ev_done_out = nullptr;
+    bool pending = false;
+  } slots[2];
   cudaStream_t streams[3] = {nullptr, nullptr, nullptr};
-  cudaEvent_t ev_in[64];
   bool ev_init = false;
 };
 
@@ -245,10 +250,12 @@ int b200mel_destroy(b200mel_handle* h) {
   cudaFree(h->d_mel_off);
   cudaFree(h->d_mel_w);
   cudaFree(h->d_dct);
-  cudaFree(h->s_pcm);
-  cudaFree(h->s_out);
-  cudaFree(h->s_small);
-  cudaFree(h->s_offsets);
+  for (auto& sl : h->slots) {
+    cudaFree(sl.s_pcm);
+    cudaFree(sl.s_out);
+    cudaFree(sl.s_small);
+    cudaFree(sl.s_offsets);
+  }
 #ifdef B200MEL_WITH_TC
   tc_plan_free(h->tc);
 #endif
@@ -256,7 +263,11 @@ int b200mel_destroy(b200mel_handle* h) {
   for (auto& s : h->streams)
     if (s) cudaStreamDestroy(s);
   if (h->ev_init)
-    for (auto& ev : h->ev_in) cudaEventDestroy(ev);
+    for (auto& sl : h->slots) {
+      for (auto& ev : sl.ev_in) cudaEventDestroy(ev);
+      cudaEventDestroy(sl.ev_done_k);
+      cudaEventDestroy(sl.ev_done_out);
+    }
   delete h;
   return B200MEL_OK;
 }
@@ -482,11 +493,28 @@ int b200mel_forward(b200mel_handle* h, const void* pcm, int32_t pcm_dtype, const
   return B200MEL_OK;
 }
 
-int b200mel_forward_host(b200mel_handle* h, const void* pcm_host, int32_t pcm_dtype, const int64_t* offsets_host,
-                         const int32_t* lengths_host, int32_t batch, int64_t row_stride, int64_t total_samples,
-                         float* out_host, int64_t t_max, int32_t* n_frames_host, uint64_t seed,
-                         uint64_t first_utterance_id, int32_t kernel) {
+static int host_wait_locked(b200mel_handle* h, int slot) {
+  b200mel_handle::HostSlot& sl = h->slots[slot];
+  if (!sl.pending) return B200MEL_OK;
+  sl.pending = false;
+  CU_CHECK(cudaEventSynchronize(sl.ev_done_k));
+  CU_CHECK(cudaEventSynchronize(sl.ev_done_out));
+  return B200MEL_OK;
+}
+
+int b200mel_forward_host_wait(b200mel_handle* h, int32_t slot) {
   if (!h) return fail(B200MEL_ERR_INVALID_ARGUMENT, "null handle");
+  if (slot < 0 || slot > 1) return fail(B200MEL_ERR_INVALID_ARGUMENT, "slot must be 0 or 1");
+  std::lock_guard<std::mutex> lock(h->host_mu);
+  return host_wait_locked(h, slot);
+}
+
+int b200mel_forward_host_submit(b200mel_handle* h, const void* pcm_host, int32_t pcm_dtype, const int64_t* offsets_host,
+                                const int32_t* lengths_host, int32_t batch, int64_t row_stride, int64_t total_samples,
+                                float* out_host, int64_t t_max, int32_t* n_frames_host, uint64_t seed,
+                                uint64_t first_utterance_id, int32_t kernel, int32_t slot) {
+  if (!h) return fail(B200MEL_ERR_INVALID_ARGUMENT, "null handle");
+  if (slot < 0 || slot > 1) return fail(B200MEL_ERR_INVALID_ARGUMENT, "slot must be 0 or 1");
   if (batch < 0 || t_max < 0 || total_samples < 0) return fail(B200MEL_ERR_INVALID_ARGUMENT, "negative size");
   if (batch == 0) return B200MEL_OK;
   if (!pcm_host || !lengths_host || (t_max > 0 && !out_host)) return fail(B200MEL_ERR_INVALID_ARGUMENT, "null buffer");
@@ -501,43 +529,53 @@ int b200mel_forward_host(b200mel_handle* h, const void* pcm_host, int32_t pcm_dt
   for (auto& s : h->streams)
     if (!s) CU_CHECK(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
   if (!h->ev_init) {
-    for (auto& ev : h->ev_in) CU_CHECK(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+    for (auto& sl : h->slots) {
+      for (auto& ev : sl.ev_in) CU_CHECK(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+      CU_CHECK(cudaEventCreateWithFlags(&sl.ev_done_k, cudaEventDisableTiming));
+      CU_CHECK(cudaEventCreateWithFlags(&sl.ev_done_out, cudaEventDisableTiming));
+    }
     h->ev_init = true;
   }
+  // the slot's previous step must have left its staging buffers (the caller has normally waited for it)
+  {
+    const int rc = host_wait_locked(h, slot);
+    if (rc != B200MEL_OK) return rc;
+  }
+  b200mel_handle::HostSlot& sl = h->slots[slot];
   const HostPlan& p = h->plan;
   const size_t pcm_bytes = static_cast<size_t>(total_samples) * esz;
   const size_t per_utt_out = static_cast<size_t>(t_max) * p.F * p.C;
   const size_t out_bytes = per_utt_out * batch * sizeof(float);
-  if (pcm_bytes > h->s_pcm_bytes) {
-    cudaFree(h->s_pcm);
-    h->s_pcm = nullptr;
-    h->s_pcm_bytes = 0;
-    CU_CHECK(cudaMalloc(&h->s_pcm, pcm_bytes + 256));
-    h->s_pcm_bytes = pcm_bytes;
+  if (pcm_bytes > sl.s_pcm_bytes) {
+    cudaFree(sl.s_pcm);
+    sl.s_pcm = nullptr;
+    sl.s_pcm_bytes = 0;
+    CU_CHECK(cudaMalloc(&sl.s_pcm, pcm_bytes + 256));
+    sl.s_pcm_bytes = pcm_bytes;
   }
-  if (out_bytes > h->s_out_bytes) {
-    cudaFree(h->s_out);
-    h->s_out = nullptr;
-    h->s_out_bytes = 0;
-    CU_CHECK(cudaMalloc(reinterpret_cast<void**>(&h->s_out), out_bytes + 256));
-    h->s_out_bytes = out_bytes;
+  if (out_bytes > sl.s_out_bytes) {
+    cudaFree(sl.s_out);
+    sl.s_out = nullptr;
+    sl.s_out_bytes = 0;
+    CU_CHECK(cudaMalloc(reinterpret_cast<void**>(&sl.s_out), out_bytes + 256));
+    sl.s_out_bytes = out_bytes;
   }
-  if (static_cast<size_t>(batch) > h->s_small_cap) {
-    cudaFree(h->s_small);
-    cudaFree(h->s_offsets);
-    h->s_small = nullptr;
-    h->s_offsets = nullptr;
-    h->s_small_cap = 0;
-    CU_CHECK(cudaMalloc(reinterpret_cast<void**>(&h->s_small), (2 * static_cast<size_t>(batch) + 4) * sizeof(int32_t)));
-    CU_CHECK(cudaMalloc(reinterpret_cast<void**>(&h->s_offsets), static_cast<size_t>(batch) * sizeof(int64_t)));
-    h->s_small_cap = batch;
+  if (static_cast<size_t>(batch) > sl.s_small_cap) {
+    cudaFree(sl.s_small);
+    cudaFree(sl.s_offsets);
+    sl.s_small = nullptr;
+    sl.s_offsets = nullptr;
+    sl.s_small_cap = 0;
+    CU_CHECK(cudaMalloc(reinterpret_cast<void**>(&sl.s_small), (2 * static_cast<size_t>(batch) + 4) * sizeof(int32_t)));
+    CU_CHECK(cudaMalloc(reinterpret_cast<void**>(&sl.s_offsets), static_cast<size_t>(batch) * sizeof(int64_t)));
+    sl.s_small_cap = batch;
   }
-  int32_t* d_len = h->s_small;
-  int32_t* d_nf = h->s_small + batch;
+  int32_t* d_len = sl.s_small;
+  int32_t* d_nf = sl.s_small + batch;
   cudaStream_t s_in = h->streams[0], s_k = h->streams[1], s_out = h->streams[2];
   CU_CHECK(cudaMemcpyAsync(d_len, lengths_host, batch * sizeof(int32_t), cudaMemcpyHostToDevice, s_in));
   if (offsets_host)
-    CU_CHECK(cudaMemcpyAsync(h->s_offsets, offsets_host, batch * sizeof(int64_t), cudaMemcpyHostToDevice, s_in));
+    CU_CHECK(cudaMemcpyAsync(sl.s_offsets, offsets_host, batch * sizeof(int64_t), cudaMemcpyHostToDevice, s_in));
 
   // Chunked 3-stage pipeline: H2D(chunk i+1) | kernel(chunk i) | D2H(chunk i-1) on three streams,
   // so PCIe traffic in both directions overlaps the kernel.
@@ -550,7 +588,7 @@ int b200mel_forward_host(b200mel_handle* h, const void* pcm_host, int32_t pcm_dt
   if (n_chunks < 1) n_chunks = 1;
   if (n_chunks > 32) n_chunks = 32;
   const char* src = static_cast<const char*>(pcm_host);
-  char* dst = static_cast<char*>(h->s_pcm);
+  char* dst = static_cast<char*>(sl.s_pcm);
   for (int c = 0; c < n_chunks; ++c) {
     const int b0 = static_cast<int>(static_cast<int64_t>(batch) * c / n_chunks);
     const int b1 = static_cast<int>(static_cast<int64_t>(batch) * (c + 1) / n_chunks);
@@ -574,28 +612,37 @@ int b200mel_forward_host(b200mel_handle* h, const void* pcm_host, int32_t pcm_dt
     if (hi > lo)
       CU_CHECK(cudaMemcpyAsync(dst + lo * esz, src + lo * esz, static_cast<size_t>(hi - lo) * esz,
                                cudaMemcpyHostToDevice, s_in));
-    CU_CHECK(cudaEventRecord(h->ev_in[2 * c], s_in));
-    CU_CHECK(cudaStreamWaitEvent(s_k, h->ev_in[2 * c], 0));
-    const int64_t* d_off = offsets_host ? h->s_offsets + b0 : nullptr;
+    CU_CHECK(cudaEventRecord(sl.ev_in[2 * c], s_in));
+    CU_CHECK(cudaStreamWaitEvent(s_k, sl.ev_in[2 * c], 0));
+    const int64_t* d_off = offsets_host ? sl.s_offsets + b0 : nullptr;
     const char* d_pcm = offsets_host ? dst : dst + static_cast<int64_t>(b0) * row_stride * esz;
     int rc = b200mel_forward(h, d_pcm, pcm_dtype, d_off, d_len + b0, b1 - b0, row_stride,
-                             h->s_out + per_utt_out * b0, t_max, d_nf + b0, nullptr, seed,
+                             sl.s_out + per_utt_out * b0, t_max, d_nf + b0, nullptr, seed,
                              first_utterance_id + static_cast<uint64_t>(b0), nullptr, kernel, s_k);
     if (rc != B200MEL_OK) return rc;
-    CU_CHECK(cudaEventRecord(h->ev_in[2 * c + 1], s_k));
-    CU_CHECK(cudaStreamWaitEvent(s_out, h->ev_in[2 * c + 1], 0));
+    CU_CHECK(cudaEventRecord(sl.ev_in[2 * c + 1], s_k));
+    CU_CHECK(cudaStreamWaitEvent(s_out, sl.ev_in[2 * c + 1], 0));
     if (per_utt_out > 0)
-      CU_CHECK(cudaMemcpyAsync(out_host + per_utt_out * b0, h->s_out + per_utt_out * b0,
+      CU_CHECK(cudaMemcpyAsync(out_host + per_utt_out * b0, sl.s_out + per_utt_out * b0,
                                per_utt_out * (b1 - b0) * sizeof(float), cudaMemcpyDeviceToHost, s_out));
   }
-  if (n_frames_host) {
-    CU_CHECK(cudaStreamSynchronize(s_k));
+  if (n_frames_host)
     CU_CHECK(cudaMemcpyAsync(n_frames_host, d_nf, batch * sizeof(int32_t), cudaMemcpyDeviceToHost, s_k));
-  }
-  CU_CHECK(cudaStreamSynchronize(s_in));
-  CU_CHECK(cudaStreamSynchronize(s_k));
-  CU_CHECK(cudaStreamSynchronize(s_out));
+  CU_CHECK(cudaEventRecord(sl.ev_done_k, s_k));
+  CU_CHECK(cudaEventRecord(sl.ev_done_out, s_out));
+  sl.pending = true;
   return B200MEL_OK;
+}
+
+int b200mel_forward_host(b200mel_handle* h, const void* pcm_host, int32_t pcm_dtype, const int64_t* offsets_host,
+                         const int32_t* lengths_host, int32_t batch, int64_t row_stride, int64_t total_samples,
+                         float* out_host, int64_t t_max, int32_t* n_frames_host, uint64_t seed,
+                         uint64_t first_utterance_id, int32_t kernel) {
+  const int rc = b200mel_forward_host_submit(h, pcm_host, pcm_dtype, offsets_host, lengths_host, batch, row_stride,
+                                             total_samples, out_host, t_max, n_frames_host, seed, first_utterance_id,
+                                             kernel, 0);
+  if (rc != B200MEL_OK) return rc;
+  return b200mel_forward_host_wait(h, 0);
 }
 
 int b200mel_specaug_draw(const int32_t* num_time, int32_t batch, int32_t v, int32_t F, int32_t m_F, int32_t T,

@@ -223,6 +223,22 @@ class FeatureFrontend:
         full PCIe speed): H2D, kernel and D2H are pipelined inside the library and the call returns
         after the result is in ``out``.  Returns (features, n_frames) as host arrays of the same kind
         as ``out`` (numpy by default)."""
+        res = self.forward_host_submit(pcm, lengths, offsets, t_max, seed, first_utterance_id, out, kernel, slot=0)
+        self.forward_host_wait(0)
+        return res
+
+    def forward_host_wait(self, slot: int = 0):
+        """Block until the step submitted on ``slot`` has delivered its host results."""
+        _lib.check(_lib.load().b200mel_forward_host_wait(self._handle, int(slot)))
+        getattr(self, "_host_pending", {}).pop(int(slot), None)
+
+    def forward_host_submit(self, pcm, lengths=None, offsets=None, t_max: Optional[int] = None, seed: int = 0,
+                            first_utterance_id: int = 0, out=None, kernel: str = "auto", slot: int = 0):
+        """``forward_host`` without the final wait: enqueue the step on staging ``slot`` (0 or 1) and return
+        ``(features, n_frames)`` - host arrays that are complete only after ``forward_host_wait(slot)``.
+        Submitting step i+1 on the other slot before waiting for step i overlaps its uploads with step i's
+        downloads (both directions of the link busy), like the reference's ``prefetch`` (run/train.py:194).
+        Pinned buffers are needed for the calls to be asynchronous."""
         pcm_np = pcm.numpy() if isinstance(pcm, torch.Tensor) else np.asarray(pcm)
         if pcm_np.dtype == np.int16:
             dt = _lib.PCM_I16
@@ -257,11 +273,15 @@ class FeatureFrontend:
             raise ValueError("out must be a C-contiguous float32 [B, t_max, F, C] array")
         n_frames = np.empty((B,), dtype=np.int32)
         vp = ctypes.c_void_p
-        _lib.check(_lib.load().b200mel_forward_host(
+        _lib.check(_lib.load().b200mel_forward_host_submit(
             self._handle, pcm_np.ctypes.data_as(vp), dt, offs.ctypes.data_as(vp) if offs is not None else None,
             lens.ctypes.data_as(vp), B, row_stride, pcm_np.size, out_np.ctypes.data_as(vp), int(t_max),
             n_frames.ctypes.data_as(vp), seed & 0xFFFFFFFFFFFFFFFF, first_utterance_id & 0xFFFFFFFFFFFFFFFF,
-            _lib.KERNELS[kernel]))
+            _lib.KERNELS[kernel], int(slot)))
+        # the library reads / writes these buffers until the wait: keep them alive
+        if not hasattr(self, "_host_pending"):
+            self._host_pending = {}
+        self._host_pending[int(slot)] = (pcm, pcm_np, lens, offs, out, out_np, n_frames)
         return out, n_frames
 
 
