@@ -96,6 +96,12 @@ struct b200mel_handle {
     int32_t* s_small = nullptr;  // lengths | n_frames | status
     int64_t* s_offsets = nullptr;
     size_t s_small_cap = 0;
+    // pinned host mirrors of the small arrays: copies from / to the caller's (usually pageable) arrays
+    // would make the asynchronous calls block
+    int32_t* p_small = nullptr;  // lengths | n_frames
+    int64_t* p_offsets = nullptr;
+    int32_t* user_n_frames = nullptr;  // where _wait delivers the frame counts
+    int32_t user_batch = 0;
     cudaEvent_t ev_in[64];
     cudaEvent_t ev_done_k = nullptr, ev_done_out = nullptr;
     bool pending = false;
@@ -255,6 +261,8 @@ int b200mel_destroy(b200mel_handle* h) {
     cudaFree(sl.s_out);
     cudaFree(sl.s_small);
     cudaFree(sl.s_offsets);
+    cudaFreeHost(sl.p_small);
+    cudaFreeHost(sl.p_offsets);
   }
 #ifdef B200MEL_WITH_TC
   tc_plan_free(h->tc);
@@ -499,6 +507,8 @@ static int host_wait_locked(b200mel_handle* h, int slot) {
   sl.pending = false;
   CU_CHECK(cudaEventSynchronize(sl.ev_done_k));
   CU_CHECK(cudaEventSynchronize(sl.ev_done_out));
+  if (sl.user_n_frames) std::memcpy(sl.user_n_frames, sl.p_small + sl.user_batch, sl.user_batch * sizeof(int32_t));
+  sl.user_n_frames = nullptr;
   return B200MEL_OK;
 }
 
@@ -509,10 +519,10 @@ int b200mel_forward_host_wait(b200mel_handle* h, int32_t slot) {
   return host_wait_locked(h, slot);
 }
 
-int b200mel_forward_host_submit(b200mel_handle* h, const void* pcm_host, int32_t pcm_dtype, const int64_t* offsets_host,
-                                const int32_t* lengths_host, int32_t batch, int64_t row_stride, int64_t total_samples,
-                                float* out_host, int64_t t_max, int32_t* n_frames_host, uint64_t seed,
-                                uint64_t first_utterance_id, int32_t kernel, int32_t slot) {
+static int host_submit(b200mel_handle* h, const void* pcm_host, int32_t pcm_dtype, const int64_t* offsets_host,
+                       const int32_t* lengths_host, int32_t batch, int64_t row_stride, int64_t total_samples,
+                       float* out_host, int64_t t_max, int32_t* n_frames_host, uint64_t seed,
+                       uint64_t first_utterance_id, int32_t kernel, int32_t slot, int default_chunks) {
   if (!h) return fail(B200MEL_ERR_INVALID_ARGUMENT, "null handle");
   if (slot < 0 || slot > 1) return fail(B200MEL_ERR_INVALID_ARGUMENT, "slot must be 0 or 1");
   if (batch < 0 || t_max < 0 || total_samples < 0) return fail(B200MEL_ERR_INVALID_ARGUMENT, "negative size");
@@ -563,9 +573,15 @@ int b200mel_forward_host_submit(b200mel_handle* h, const void* pcm_host, int32_t
   if (static_cast<size_t>(batch) > sl.s_small_cap) {
     cudaFree(sl.s_small);
     cudaFree(sl.s_offsets);
+    cudaFreeHost(sl.p_small);
+    cudaFreeHost(sl.p_offsets);
     sl.s_small = nullptr;
     sl.s_offsets = nullptr;
+    sl.p_small = nullptr;
+    sl.p_offsets = nullptr;
     sl.s_small_cap = 0;
+    CU_CHECK(cudaMallocHost(reinterpret_cast<void**>(&sl.p_small), (2 * static_cast<size_t>(batch) + 4) * sizeof(int32_t)));
+    CU_CHECK(cudaMallocHost(reinterpret_cast<void**>(&sl.p_offsets), static_cast<size_t>(batch) * sizeof(int64_t)));
     CU_CHECK(cudaMalloc(reinterpret_cast<void**>(&sl.s_small), (2 * static_cast<size_t>(batch) + 4) * sizeof(int32_t)));
     CU_CHECK(cudaMalloc(reinterpret_cast<void**>(&sl.s_offsets), static_cast<size_t>(batch) * sizeof(int64_t)));
     sl.s_small_cap = batch;
@@ -573,16 +589,21 @@ int b200mel_forward_host_submit(b200mel_handle* h, const void* pcm_host, int32_t
   int32_t* d_len = sl.s_small;
   int32_t* d_nf = sl.s_small + batch;
   cudaStream_t s_in = h->streams[0], s_k = h->streams[1], s_out = h->streams[2];
-  CU_CHECK(cudaMemcpyAsync(d_len, lengths_host, batch * sizeof(int32_t), cudaMemcpyHostToDevice, s_in));
-  if (offsets_host)
-    CU_CHECK(cudaMemcpyAsync(sl.s_offsets, offsets_host, batch * sizeof(int64_t), cudaMemcpyHostToDevice, s_in));
+  std::memcpy(sl.p_small, lengths_host, batch * sizeof(int32_t));
+  CU_CHECK(cudaMemcpyAsync(d_len, sl.p_small, batch * sizeof(int32_t), cudaMemcpyHostToDevice, s_in));
+  if (offsets_host) {
+    std::memcpy(sl.p_offsets, offsets_host, batch * sizeof(int64_t));
+    CU_CHECK(cudaMemcpyAsync(sl.s_offsets, sl.p_offsets, batch * sizeof(int64_t), cudaMemcpyHostToDevice, s_in));
+  }
 
   // Chunked 3-stage pipeline: H2D(chunk i+1) | kernel(chunk i) | D2H(chunk i-1) on three streams,
   // so PCIe traffic in both directions overlaps the kernel.
-  // 8 chunks: measured best on B200 (4: 1.20M, 8: 1.26M, 16: 1.23M, 32: 1.11M audio-s/s); the call is
-  // PCIe-bound (123 MB each way, ~40 GB/s per direction when both directions run).
+  // Chunks per step, measured on B200 (123 MB each way): a lone synchronous call is fastest with 8
+  // (4: 1.20 M, 8: 1.28 M, 16: 1.23 M, 32: 1.11 M audio-s/s - the first upload and the last download cannot
+  // overlap anything); back-to-back submits overlap across steps and are fastest with 2 (1: 1.43 M, 2: 1.47 M,
+  // 4: 1.45 M, 8: 1.40 M).  The link carries ~49 GB/s per direction when both directions run.
   // B200MEL_HOST_CHUNKS overrides (developer knob for the e2e measurement).
-  int n_chunks = 8;
+  int n_chunks = default_chunks;
   if (const char* env = getenv("B200MEL_HOST_CHUNKS")) n_chunks = atoi(env);
   if (n_chunks > batch) n_chunks = batch;
   if (n_chunks < 1) n_chunks = 1;
@@ -627,20 +648,29 @@ int b200mel_forward_host_submit(b200mel_handle* h, const void* pcm_host, int32_t
                                per_utt_out * (b1 - b0) * sizeof(float), cudaMemcpyDeviceToHost, s_out));
   }
   if (n_frames_host)
-    CU_CHECK(cudaMemcpyAsync(n_frames_host, d_nf, batch * sizeof(int32_t), cudaMemcpyDeviceToHost, s_k));
+    CU_CHECK(cudaMemcpyAsync(sl.p_small + batch, d_nf, batch * sizeof(int32_t), cudaMemcpyDeviceToHost, s_k));
+  sl.user_n_frames = n_frames_host;
+  sl.user_batch = batch;
   CU_CHECK(cudaEventRecord(sl.ev_done_k, s_k));
   CU_CHECK(cudaEventRecord(sl.ev_done_out, s_out));
   sl.pending = true;
   return B200MEL_OK;
 }
 
+int b200mel_forward_host_submit(b200mel_handle* h, const void* pcm_host, int32_t pcm_dtype, const int64_t* offsets_host,
+                                const int32_t* lengths_host, int32_t batch, int64_t row_stride, int64_t total_samples,
+                                float* out_host, int64_t t_max, int32_t* n_frames_host, uint64_t seed,
+                                uint64_t first_utterance_id, int32_t kernel, int32_t slot) {
+  return host_submit(h, pcm_host, pcm_dtype, offsets_host, lengths_host, batch, row_stride, total_samples, out_host,
+                     t_max, n_frames_host, seed, first_utterance_id, kernel, slot, 2);
+}
+
 int b200mel_forward_host(b200mel_handle* h, const void* pcm_host, int32_t pcm_dtype, const int64_t* offsets_host,
                          const int32_t* lengths_host, int32_t batch, int64_t row_stride, int64_t total_samples,
                          float* out_host, int64_t t_max, int32_t* n_frames_host, uint64_t seed,
                          uint64_t first_utterance_id, int32_t kernel) {
-  const int rc = b200mel_forward_host_submit(h, pcm_host, pcm_dtype, offsets_host, lengths_host, batch, row_stride,
-                                             total_samples, out_host, t_max, n_frames_host, seed, first_utterance_id,
-                                             kernel, 0);
+  const int rc = host_submit(h, pcm_host, pcm_dtype, offsets_host, lengths_host, batch, row_stride, total_samples,
+                             out_host, t_max, n_frames_host, seed, first_utterance_id, kernel, 0, 8);
   if (rc != B200MEL_OK) return rc;
   return b200mel_forward_host_wait(h, 0);
 }
