@@ -120,6 +120,19 @@ class ClockSampler:
                 "samples": len(self.samples)}
 
 
+_JSON_FD = []  # the real stdout, saved while fd 1 points at stderr (multi-rank runs)
+
+
+def emit_line(line):
+    text = json.dumps(line) + "\n"
+    if _JSON_FD:
+        sys.stdout.flush()
+        os.write(_JSON_FD[0], text.encode())
+    else:
+        sys.stdout.write(text)
+        sys.stdout.flush()
+
+
 def cpu_reference_run(n_utt, steps, warmup, threads=0):
     """Time the oracle's C restatement of the reference's TF CPU path (kind = "port": TensorFlow
     cannot be installed here) on `n_utt` utterances of the same workload per step."""
@@ -194,6 +207,11 @@ def main():
     if world > 1:
         import torch.distributed as dist
 
+        # libnccl prints its version banner on fd 1 at the first communicator: keep rank 0's stdout to the
+        # one JSON line by pointing fd 1 at stderr until the line is printed
+        sys.stdout.flush()
+        _JSON_FD.append(os.dup(1))
+        os.dup2(2, 1)
         dist.init_process_group("nccl", device_id=dev)
 
     fe = FeatureFrontend("log-mel-spectrogram", **CFG, device=dev)
@@ -309,7 +327,7 @@ def main():
                                               "path; TensorFlow not installable here)" % (n_utt, reps)}
         except Exception as e:  # the baseline is informational; never lose the GPU numbers to it
             line["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": 0, "kind": "port", "sample": "failed: %r" % (e,)}
-    print(json.dumps(line), flush=True)
+    emit_line(line)
     if dist is not None:
         dist.barrier()
         dist.destroy_process_group()
