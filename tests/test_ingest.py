@@ -210,3 +210,39 @@ def test_load_audio_file_wrapper_and_frontend_chain(ing, tmp_path):
     out, nf = fe(pcm, lengths=lengths)
     g = np.load(os.path.join(GOLDEN_DIR, "ref_wav_dataset_tfrecord.npz"))
     assert nf.tolist() == [412, 412] and np.array_equal(out[0].cpu().numpy(), g["feature_0"])
+
+
+@gpu
+def test_full_size_round_trip_and_mask_property(ing):
+    """BASELINE config-2 size (256 x 15 s) through size-independent properties: ingest(bytes) gives back the
+    samples bit for bit for every payload alignment; without SpecAugment the models' padding mask of the
+    front-end's batch is exactly `any frame of the stride group < n_frames`."""
+    import speech_recognition_b200 as pkg
+    from speech_recognition_b200 import batching
+
+    B, L = 256, 240000
+    rng = np.random.default_rng(11)
+    x = rng.integers(-32768, 32768, (B, L), dtype=np.int16)
+    lens = rng.integers(160, L + 1, B)
+    lens[:4] = [L, 0, 319, 320]
+    header = wav_image(np.zeros(0, np.int16))[:40]
+    images = []
+    for b in range(B):
+        body = x[b, :lens[b]].astype("<i2").tobytes()
+        pad = b"z" * (b % 5)                                   # odd / even junk chunks shift the payload alignment
+        extra = (b"LIST" + struct.pack("<I", len(pad)) + pad + (b"\x00" if len(pad) & 1 else b"")) if pad else b""
+        img = header[:36] + extra + b"data" + struct.pack("<I", len(body)) + body
+        images.append(img[:4] + struct.pack("<I", len(img) - 8) + img[8:])
+    pcm, lengths = ing.ingest_file_images(images, "wav", row_stride=L)
+    torch.cuda.synchronize()
+    assert lengths.cpu().numpy().tolist() == lens.tolist()
+    got = pcm.cpu().numpy()
+    valid = np.arange(L)[None, :] < lens[:, None]
+    assert np.array_equal(got[valid], x[valid]) and not got[~valid].any()
+
+    fe = pkg.FeatureFrontend("log-mel-spectrogram", **LIBRI)
+    feats, nf = fe(pcm, lengths=lengths)
+    mask = batching.audio_mask(feats, [3, 3], [2, 2]).cpu().numpy()
+    nfr = np.minimum(nf.cpu().numpy(), feats.shape[1])
+    want = (np.arange(mask.shape[1])[None, :] * 4) < nfr[:, None]
+    assert mask.shape == (B, 374) and np.array_equal(mask, want)
