@@ -62,7 +62,10 @@ def _payload(file_format: str, image: np.ndarray) -> Tuple[int, int, int]:
                          % (h.format, h.bits_per_sample))
     if h.channels < 1 or h.channels > 256:
         raise ValueError("wav: %d channels" % h.channels)
-    return h.data_offset, h.data_bytes, h.channels
+    # whole sample frames only (a trailing partial frame of a damaged file is dropped, like a WAV decoder does;
+    # the zero-byte padding of odd lengths is the raw-pcm rule of data.py:102-103, not a WAV rule)
+    frame = 2 * h.channels
+    return h.data_offset, h.data_bytes // frame * frame, h.channels
 
 
 def _ptr(t: Optional[torch.Tensor]):

@@ -168,6 +168,11 @@ def test_dense_truncation_and_unsupported_wav(ing):
     torch.cuda.synchronize()
     assert pcm.shape == (2, 640) and lengths.tolist() == [640, 10]
     assert np.array_equal(pcm[0].cpu().numpy(), x[:640])
+    # a damaged file whose data chunk ends inside a sample frame: the partial frame is dropped
+    cut = wav_image(x)[:-1]
+    pcm, lengths = ing.ingest_file_images([cut], "wav")
+    torch.cuda.synchronize()
+    assert lengths.tolist() == [999] and np.array_equal(pcm[0, :999].cpu().numpy(), x[:999])
     img8 = bytearray(wav_image(x))
     img8[34:36] = struct.pack("<H", 8)
     with pytest.raises(ValueError, match="16-bit"):
