@@ -259,6 +259,8 @@ def main():
     for i in range(2):
         fe.forward_host(host_in[i % 2], out=host_out[i % 2], kernel=args.kernel)
     # (a) synchronous call per step: upload, kernels, download, return
+    if dist is not None:
+        dist.barrier()
     torch.cuda.synchronize()
     t0 = time.perf_counter()
     for i in range(e2e_steps):
@@ -283,7 +285,16 @@ def main():
     te = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
     if dist is not None:
         dist.all_reduce(te, op=dist.ReduceOp.MAX)
-    e2e_value = world * e2e_steps * AUDIO_S_PER_STEP / float(te.item())
+    e2e_stream_value = world * e2e_steps * AUDIO_S_PER_STEP / float(te.item())
+    ts = torch.tensor([e2e_sync_s], dtype=torch.float64, device=dev)
+    if dist is not None:
+        dist.all_reduce(ts, op=dist.ReduceOp.MAX)
+    e2e_sync_value = world * e2e_steps * AUDIO_S_PER_STEP / float(ts.item())
+    # both forms move every step's input up and its result down inside the timed region; the line's value is
+    # the faster one on this box (the streaming form wins on 1-2 GPUs, the synchronous call when 8 ranks share
+    # the host's memory system), both are listed
+    e2e_value = max(e2e_stream_value, e2e_sync_value)
+    e2e_form = "submit/wait on two staging slots" if e2e_stream_value >= e2e_sync_value else "synchronous call"
 
     if rank != 0:
         if dist is not None:
@@ -310,8 +321,8 @@ def main():
                      "launch_us": per_launch_s * 1e6},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": B * L * 2, "d2h_bytes_per_step": B * T * 80 * 4,
                 "steps": e2e_steps,
-                "timer": "host wall clock around the loop of C-ABI submit / wait calls (two staging slots), max over ranks",
-                "sync_call_value": world * e2e_steps * AUDIO_S_PER_STEP / e2e_sync_s,
+                "timer": "host wall clock around the loop of C-ABI calls, max over ranks",
+                "form": e2e_form, "stream_value": e2e_stream_value, "sync_call_value": e2e_sync_value,
                 "checksum": checksum},
         "gpu_launches": int(launches),
         "clocks": clocks,

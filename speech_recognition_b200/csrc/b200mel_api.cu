@@ -816,8 +816,8 @@ int b200mel_audio_mask(const float* feat, int32_t batch, int64_t t_max, int64_t 
   if (batch == 0 || reduced == 0) return B200MEL_OK;
   if (!feat || !mask_out) return fail(B200MEL_ERR_INVALID_ARGUMENT, "null buffer");
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-  // one warp per entry, at most one resident wave (148 SMs x 8 blocks of 8 warps)
-  const int64_t want = (static_cast<int64_t>(batch) * reduced + 7) / 8;
+  // one warp per pair of entries, at most one resident wave (148 SMs x 8 blocks of 8 warps)
+  const int64_t want = (static_cast<int64_t>(batch) * ((reduced + 1) / 2) + 7) / 8;
   const unsigned bx = static_cast<unsigned>(std::min<int64_t>(want, 1184));
   audio_mask_kernel<<<bx, 256, 0, st>>>(feat, batch, t_max, row_elems, group, reduced, mask_out);
   cudaError_t e = cudaGetLastError();

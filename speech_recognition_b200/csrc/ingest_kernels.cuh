@@ -147,37 +147,51 @@ ingest_multi_kernel(const uint8_t* __restrict__ bytes, const int64_t* __restrict
 // _audio_mask (models/las.py:205-217, models/deepspeech2.py:68-78): frame t is "real" when any of its
 // F*C values differs from the pad value 0 (so -0.0 and +0.0 both count as padding, NaN as real);
 // group consecutive frames by the product of the convolution time strides and OR them.
-// One warp per output entry over a flat grid-stride loop of all B * reduced entries (one resident wave),
-// 128-bit loads when the row group is 16-byte aligned, two in flight per lane.
+// A warp takes a PAIR of consecutive entries of one utterance - 2 * group frames, contiguous in memory - as one
+// stream of 128-bit loads (five independent loads per lane at F*C = 80, group = 4), over a flat grid-stride
+// loop of all pairs (one resident wave).
 __global__ void __launch_bounds__(256)
 audio_mask_kernel(const float* __restrict__ feat, int batch, int64_t t_max, int64_t row_elems, int group, int64_t reduced,
                   uint8_t* __restrict__ mask) {
   const int lane = threadIdx.x & 31;
   const int64_t warps = (static_cast<int64_t>(gridDim.x) * blockDim.x) >> 5;
-  const int64_t n = static_cast<int64_t>(group) * row_elems;
-  const int64_t total = static_cast<int64_t>(batch) * reduced;
+  const int64_t n = static_cast<int64_t>(group) * row_elems;  // floats per entry
+  const int64_t pairs = (reduced + 1) >> 1;
+  const int64_t total = static_cast<int64_t>(batch) * pairs;
   for (int64_t e = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5; e < total; e += warps) {
-    const int64_t b = e / reduced, r = e - b * reduced;
+    const int64_t b = e / pairs, r = 2 * (e - b * pairs);
+    const bool two = r + 1 < reduced;
     const float* p = feat + (b * t_max + r * group) * row_elems;
-    bool any = false;
+    const int64_t len = two ? 2 * n : n;
+    bool any0 = false, any1 = false;
     if (((reinterpret_cast<uintptr_t>(p) & 15) == 0) && (n & 3) == 0) {
       const float4* q = reinterpret_cast<const float4*>(p);
-      const int64_t n4 = n >> 2;
+      const int64_t n4 = n >> 2, len4 = len >> 2;
       int64_t i = lane;
-      for (; i + 32 < n4; i += 64) {
-        const float4 v = __ldg(q + i), w = __ldg(q + i + 32);
-        any |= (v.x != 0.0f) | (v.y != 0.0f) | (v.z != 0.0f) | (v.w != 0.0f) | (w.x != 0.0f) | (w.y != 0.0f) |
-               (w.z != 0.0f) | (w.w != 0.0f);
+      for (; i + 64 < len4; i += 96) {
+        const float4 u = __ldg(q + i), v = __ldg(q + i + 32), w = __ldg(q + i + 64);
+        const bool zu = (u.x != 0.0f) | (u.y != 0.0f) | (u.z != 0.0f) | (u.w != 0.0f);
+        const bool zv = (v.x != 0.0f) | (v.y != 0.0f) | (v.z != 0.0f) | (v.w != 0.0f);
+        const bool zw = (w.x != 0.0f) | (w.y != 0.0f) | (w.z != 0.0f) | (w.w != 0.0f);
+        any0 |= (zu & (i < n4)) | (zv & (i + 32 < n4)) | (zw & (i + 64 < n4));
+        any1 |= (zu & (i >= n4)) | (zv & (i + 32 >= n4)) | (zw & (i + 64 >= n4));
       }
-      if (i < n4) {
-        const float4 v = __ldg(q + i);
-        any |= (v.x != 0.0f) | (v.y != 0.0f) | (v.z != 0.0f) | (v.w != 0.0f);
+      for (; i < len4; i += 32) {
+        const float4 u = __ldg(q + i);
+        const bool zu = (u.x != 0.0f) | (u.y != 0.0f) | (u.z != 0.0f) | (u.w != 0.0f);
+        any0 |= zu & (i < n4);
+        any1 |= zu & (i >= n4);
       }
     } else {
-      for (int64_t i = lane; i < n; i += 32) any |= (__ldg(p + i) != 0.0f);
+      for (int64_t i = lane; i < len; i += 32) {
+        const bool z = __ldg(p + i) != 0.0f;
+        any0 |= z & (i < n);
+        any1 |= z & (i >= n);
+      }
     }
-    const unsigned m = __ballot_sync(0xFFFFFFFFu, any);
-    if (lane == 0) mask[e] = m ? 1 : 0;
+    const unsigned m0 = __ballot_sync(0xFFFFFFFFu, any0), m1 = __ballot_sync(0xFFFFFFFFu, any1);
+    if (lane == 0) mask[b * reduced + r] = m0 ? 1 : 0;
+    if (lane == 1 && two) mask[b * reduced + r + 1] = m1 ? 1 : 0;
   }
 }
 
