@@ -120,7 +120,10 @@ int64_t b200mel_launch_count(const b200mel_handle* handle);
  *              to draw them from Philox4x32-10 keyed by (seed, first_utterance_id + b)
  *              (same stream as b200mel_specaug_draw).  Ignored unless spec_augment_enable.
  *   status     device int32[1] or NULL: OR-ed with 1 if a draw hit TF's `maxval <= minval` error
- *              case (the mask is then empty).
+ *              case (the mask is then empty; tf.random.uniform raises there, data.py:284-285, 297),
+ *              with 0x100 if a pipeline wait inside the tensor-core kernel timed out (a bug, never
+ *              a hang).  The call is asynchronous: a caller that wants the reference's error
+ *              behaviour reads the word after synchronising; the host-buffer calls below do it.
  */
 int b200mel_forward(b200mel_handle* handle, const void* pcm, int32_t pcm_dtype,
                     const int64_t* offsets, const int32_t* lengths, int32_t batch,
@@ -130,7 +133,9 @@ int b200mel_forward(b200mel_handle* handle, const void* pcm, int32_t pcm_dtype,
 
 /* Same computation with HOST buffers: pinned staging, H2D copy, kernel, D2H copy, synchronised on
  * return.  This is the call the end-to-end (e2e) throughput is measured through.  offsets may be
- * NULL (dense).  n_frames may be NULL. */
+ * NULL (dense).  n_frames may be NULL.  The step's status word comes back with the results: the call
+ * (or _wait) returns B200MEL_ERR_INVALID_ARGUMENT when a SpecAugment draw was invalid (the reference
+ * raises), B200MEL_ERR_CUDA on a kernel protocol timeout; `out_host` is complete in both cases. */
 int b200mel_forward_host(b200mel_handle* handle, const void* pcm_host, int32_t pcm_dtype,
                          const int64_t* offsets_host, const int32_t* lengths_host, int32_t batch,
                          int64_t row_stride, int64_t total_samples, float* out_host, int64_t t_max,

@@ -96,6 +96,10 @@ def assemble_batch(frontend, pcm, lengths, token_lengths: Optional[torch.Tensor]
             t_max = frontend.num_frames(int(host.max())) if host.size else 0
         t_max = min(int(t_max), int(max_audio_length))
     feats, n_frames = frontend(pcm, lengths=lengths, t_max=t_max, **forward_kwargs)
+    if audio_pad_length is not None and feats.shape[1] < int(audio_pad_length):
+        # "slice" below the padded length: the reference slices each example (data.py:345-354) and
+        # padded_batch then pads to audio_pad_length (run/train.py:182-197) - zeros behind the slice
+        feats = torch.nn.functional.pad(feats, (0, 0, 0, 0, 0, int(audio_pad_length) - feats.shape[1]))
     out = {"features": feats, "n_frames": n_frames}
     keep = torch.ones_like(n_frames, dtype=torch.bool)
     if max_over_policy == "filter":
@@ -104,7 +108,7 @@ def assemble_batch(frontend, pcm, lengths, token_lengths: Optional[torch.Tensor]
                               max_token_length if max_token_length is not None else 2 ** 31 - 1)(
             n_frames, tl.to(n_frames.device))
     elif max_over_policy == "slice":
-        out["n_frames"] = torch.clamp(n_frames, max=feats.shape[1])
+        out["n_frames"] = torch.clamp(n_frames, max=int(t_max))
     out["keep"] = keep
     if mask_layers is not None:
         out["mask"] = audio_mask(feats, mask_layers[0], mask_layers[1])

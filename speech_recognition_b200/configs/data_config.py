@@ -1,4 +1,7 @@
-"""Mirror of the reference's DataConfig (speech_recognition/configs/data_config.py:10-106).
+"""DataConfig / SpecAugmentConfig: the config SCHEMA IS REPRODUCED FROM THE REFERENCE
+(speech_recognition/configs/data_config.py:10-106) key for key - field names, defaults, validation and
+properties are the drop-in contract of SURVEY 8(b), not original work; only the callables they return
+(this package's CUDA-backed front-end) are.
 
 Same YAML keys, validation and properties, so ``resources/configs/{libri,kspon,clovacall}_config.yml``
 load unmodified.  ``audio_feature_fn`` returns this package's CUDA-backed per-example callables;

@@ -48,6 +48,15 @@ cudaError_t upload(const std::vector<T>& v, T** dptr) {
   return cudaMemcpy(*dptr, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice);
 }
 
+// Stream-ordered scratch that must be released on every path out of a function (error returns included).
+struct AsyncScratch {
+  void* p = nullptr;
+  cudaStream_t st = nullptr;
+  ~AsyncScratch() {
+    if (p) cudaFreeAsync(p, st);
+  }
+};
+
 struct DeviceGuard {
   int prev = -1;
   bool ok = true;
@@ -184,8 +193,10 @@ int b200mel_create(const b200mel_config* config, int device, b200mel_handle** ou
   h->g_warps = warps;
   h->g_ft = ft;
   h->g_smem = smem_need(warps, ft);
+  // The attribute belongs to the (function, device) pair, not to the handle: a later handle with a
+  // smaller tile would lower the cap under an earlier one.  Always raise it to the device maximum.
   e = cudaFuncSetAttribute(generic_frontend_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                           static_cast<int>(h->g_smem));
+                           h->max_smem_optin > 0 ? h->max_smem_optin : static_cast<int>(h->g_smem));
   if (e != cudaSuccess) {
     b200mel_destroy(h);
     return cuda_fail(e, "cudaFuncSetAttribute(generic_frontend_kernel)");
@@ -235,7 +246,7 @@ int b200mel_create(const b200mel_config* config, int device, b200mel_handle** ou
   if (h->tc_ok && p.cfg.audio_feature_type == B200MEL_FEATURE_MFCC) {
     const size_t smem = mfcc_post_smem_bytes(p.cfg.num_mel_bins, p.n_mfcc_eff);
     if (p.cfg.num_mel_bins > kMfccMaxM || p.n_mfcc_eff > kMfccMaxC || smem > static_cast<size_t>(h->max_smem_optin) ||
-        cudaFuncSetAttribute(mfcc_post_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)) != cudaSuccess) {
+        cudaFuncSetAttribute(mfcc_post_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem_optin) != cudaSuccess) {
       cudaGetLastError();
       h->tc_ok = false;
     }
@@ -408,7 +419,9 @@ int b200mel_forward(b200mel_handle* h, const void* pcm, int32_t pcm_dtype, const
     return fail(B200MEL_ERR_UNSUPPORTED, "t_max is too large for the tensor-core kernel (use B200MEL_KERNEL_GENERIC)");
   // float32 PCM, dense rows, kernel = auto: convert to int16 when that is exact (the reference's audio
   // is int16 / 32768, data.py:98-116) and gate the two kernels on the outcome - no host round trip
-  void* f32_scratch = nullptr;
+  AsyncScratch f32_guard;  // (freed behind both kernels of the pair, and on every error return)
+  f32_guard.st = st;
+  void*& f32_scratch = f32_guard.p;
   const KernelParams kp_f32 = kp;
   const bool f32_gated = h->tc_ok && kernel == B200MEL_KERNEL_AUTO && t_max > 0 && pcm_dtype == B200MEL_PCM_F32 && !offsets &&
                          tc_aligned && kp.n_masks_f + kp.n_masks_t <= 16 && tc_fits && row_stride > 0;
@@ -493,9 +506,6 @@ int b200mel_forward(b200mel_handle* h, const void* pcm, int32_t pcm_dtype, const
   dim3 grid(static_cast<unsigned>(tiles), static_cast<unsigned>(batch));
   generic_frontend_kernel<<<grid, h->g_warps * 32, h->g_smem, st>>>(kp);
   cudaError_t e = cudaGetLastError();
-#ifdef B200MEL_WITH_TC
-  if (f32_scratch) cudaFreeAsync(f32_scratch, st);  // (stream-ordered: after both kernels of the pair)
-#endif
   if (e != cudaSuccess) return cuda_fail(e, "generic_frontend_kernel launch");
   h->launches.fetch_add(1);
   return B200MEL_OK;
@@ -509,6 +519,15 @@ static int host_wait_locked(b200mel_handle* h, int slot) {
   CU_CHECK(cudaEventSynchronize(sl.ev_done_out));
   if (sl.user_n_frames) std::memcpy(sl.user_n_frames, sl.p_small + sl.user_batch, sl.user_batch * sizeof(int32_t));
   sl.user_n_frames = nullptr;
+  // the step's device status word (b200mel_forward's `status`), delivered with the frame counts: the
+  // results are in place, but the reference would have raised on this batch
+  const int32_t st_word = sl.p_small[2 * sl.user_batch];
+  if (st_word & 0x100)
+    return fail(B200MEL_ERR_CUDA, "tensor-core kernel: a pipeline wait timed out (internal protocol error)");
+  if (st_word & 1)
+    return fail(B200MEL_ERR_INVALID_ARGUMENT,
+                "SpecAugment: a draw had maxval <= minval (F > frequency_dim, or an utterance with too few frames); "
+                "tf.random.uniform raises here (data.py:284-285, 297) - the mask was left empty");
   return B200MEL_OK;
 }
 
@@ -588,8 +607,11 @@ static int host_submit(b200mel_handle* h, const void* pcm_host, int32_t pcm_dtyp
   }
   int32_t* d_len = sl.s_small;
   int32_t* d_nf = sl.s_small + batch;
+  int32_t* d_status = sl.s_small + 2 * static_cast<size_t>(batch);
   cudaStream_t s_in = h->streams[0], s_k = h->streams[1], s_out = h->streams[2];
   std::memcpy(sl.p_small, lengths_host, batch * sizeof(int32_t));
+  sl.p_small[2 * static_cast<size_t>(batch)] = 0;
+  CU_CHECK(cudaMemsetAsync(d_status, 0, sizeof(int32_t), s_in));  // (every kernel of the step waits for s_in)
   CU_CHECK(cudaMemcpyAsync(d_len, sl.p_small, batch * sizeof(int32_t), cudaMemcpyHostToDevice, s_in));
   if (offsets_host) {
     std::memcpy(sl.p_offsets, offsets_host, batch * sizeof(int64_t));
@@ -603,8 +625,11 @@ static int host_submit(b200mel_handle* h, const void* pcm_host, int32_t pcm_dtyp
   // overlap anything); back-to-back submits overlap across steps and are fastest with 2 (1: 1.43 M, 2: 1.47 M,
   // 4: 1.45 M, 8: 1.40 M).  The link carries ~49 GB/s per direction when both directions run.
   // B200MEL_HOST_CHUNKS overrides (developer knob for the e2e measurement).
-  int n_chunks = default_chunks;
-  if (const char* env = getenv("B200MEL_HOST_CHUNKS")) n_chunks = atoi(env);
+  static const int forced_chunks = [] {
+    const char* env = getenv("B200MEL_HOST_CHUNKS");
+    return env ? atoi(env) : 0;
+  }();
+  int n_chunks = forced_chunks > 0 ? forced_chunks : default_chunks;
   if (n_chunks > batch) n_chunks = batch;
   if (n_chunks < 1) n_chunks = 1;
   if (n_chunks > 32) n_chunks = 32;
@@ -639,7 +664,7 @@ static int host_submit(b200mel_handle* h, const void* pcm_host, int32_t pcm_dtyp
     const char* d_pcm = offsets_host ? dst : dst + static_cast<int64_t>(b0) * row_stride * esz;
     int rc = b200mel_forward(h, d_pcm, pcm_dtype, d_off, d_len + b0, b1 - b0, row_stride,
                              sl.s_out + per_utt_out * b0, t_max, d_nf + b0, nullptr, seed,
-                             first_utterance_id + static_cast<uint64_t>(b0), nullptr, kernel, s_k);
+                             first_utterance_id + static_cast<uint64_t>(b0), d_status, kernel, s_k);
     if (rc != B200MEL_OK) return rc;
     CU_CHECK(cudaEventRecord(sl.ev_in[2 * c + 1], s_k));
     CU_CHECK(cudaStreamWaitEvent(s_out, sl.ev_in[2 * c + 1], 0));
@@ -647,8 +672,8 @@ static int host_submit(b200mel_handle* h, const void* pcm_host, int32_t pcm_dtyp
       CU_CHECK(cudaMemcpyAsync(out_host + per_utt_out * b0, sl.s_out + per_utt_out * b0,
                                per_utt_out * (b1 - b0) * sizeof(float), cudaMemcpyDeviceToHost, s_out));
   }
-  if (n_frames_host)
-    CU_CHECK(cudaMemcpyAsync(sl.p_small + batch, d_nf, batch * sizeof(int32_t), cudaMemcpyDeviceToHost, s_k));
+  // frame counts and the status word behind them, in one copy
+  CU_CHECK(cudaMemcpyAsync(sl.p_small + batch, d_nf, (static_cast<size_t>(batch) + 1) * sizeof(int32_t), cudaMemcpyDeviceToHost, s_k));
   sl.user_n_frames = n_frames_host;
   sl.user_batch = batch;
   CU_CHECK(cudaEventRecord(sl.ev_done_k, s_k));

@@ -40,7 +40,6 @@ __device__ __forceinline__ bool mbar_wait(uint64_t* bar, uint32_t parity) {
   }
   return false;
 }
-__device__ __forceinline__ bool mbar_wait_relaxed(uint64_t* bar, uint32_t parity) { return mbar_wait(bar, parity); }
 
 // Shared-memory matrix descriptor (tcgen05 "smem descriptor"): start address, leading / stride byte
 // offsets (all >> 4), version 1, swizzle mode in bits [61,64).

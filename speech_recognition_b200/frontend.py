@@ -129,12 +129,21 @@ class FeatureFrontend:
     # ------------------------------------------------------------------------------------------
     def __call__(self, pcm: torch.Tensor, lengths=None, offsets=None, t_max: Optional[int] = None,
                  seed: int = 0, first_utterance_id: int = 0, mask_table: Optional[torch.Tensor] = None,
-                 out: Optional[torch.Tensor] = None, kernel: str = "auto", return_status: bool = False
-                 ) -> Tuple[torch.Tensor, torch.Tensor]:
+                 out: Optional[torch.Tensor] = None, kernel: str = "auto", return_status: bool = False,
+                 validate: bool = False) -> Tuple[torch.Tensor, torch.Tensor]:
         """pcm: CUDA int16 or float32; dense [B, L] (``lengths`` optional) or ragged 1-D with
         ``offsets`` [B] (int64, element offsets) and ``lengths`` [B].  Returns
         (features [B, t_max, F, C] float32, n_frames [B] int32), both on the device; padding
-        frames are exactly +0.0.  Asynchronous on the current torch stream."""
+        frames are exactly +0.0.  Asynchronous on the current torch stream.
+
+        Preconditions.  Host-side ``lengths`` / ``offsets`` are range-checked here.  Device-side ones
+        are NOT looked at (that would be a stream synchronisation per call): the caller guarantees
+        ``0 <= lengths[b]`` and ``offsets[b] + lengths[b] <= pcm.numel()`` (dense: ``lengths[b] <= L``),
+        or passes ``validate=True`` to have them checked on the device (one synchronisation).
+        SpecAugment draws the reference would raise on (``tf.random.uniform`` with maxval <= minval:
+        ``F`` above the feature width, an utterance with fewer frames than a drawn ``t``) leave that
+        mask empty and set bit 0 of the device status word: pass ``return_status=True`` and read it
+        to get the reference's error behaviour; ``forward_host`` does this itself and raises."""
         if not pcm.is_cuda or pcm.device != self.device:
             raise RuntimeError("pcm must live on %s (got %s): there is no CPU path" % (self.device, pcm.device))
         if pcm.dtype == torch.int16:
@@ -170,10 +179,18 @@ class FeatureFrontend:
             d_lengths = torch.from_numpy(host_lengths.astype(np.int32)).to(self.device, non_blocking=True)
         else:
             d_lengths = lengths.to(torch.int32).contiguous()
+            if validate and B:
+                lo, hi = int(d_lengths.min()), int(d_lengths.max())
+                if lo < 0 or (offsets is None and hi > L):
+                    raise ValueError("lengths outside [0, L]")
         d_offsets = None
         if offsets is not None:
             if isinstance(offsets, torch.Tensor) and offsets.is_cuda:
                 d_offsets = offsets.to(torch.int64).contiguous()
+                if validate and B:
+                    end = d_offsets + d_lengths.to(torch.int64)
+                    if int(d_offsets.min()) < 0 or int(end.max()) > L:
+                        raise ValueError("offsets/lengths outside the pcm buffer")
             else:
                 ho = np.asarray(offsets.cpu() if isinstance(offsets, torch.Tensor) else offsets, dtype=np.int64)
                 if host_lengths is not None and ho.size and (ho.min() < 0 or (ho + host_lengths).max() > L):
@@ -229,8 +246,10 @@ class FeatureFrontend:
 
     def forward_host_wait(self, slot: int = 0):
         """Block until the step submitted on ``slot`` has delivered its host results."""
-        _lib.check(_lib.load().b200mel_forward_host_wait(self._handle, int(slot)))
-        getattr(self, "_host_pending", {}).pop(int(slot), None)
+        try:
+            _lib.check(_lib.load().b200mel_forward_host_wait(self._handle, int(slot)))
+        finally:   # (the results are delivered even when the step's status word makes the call raise)
+            getattr(self, "_host_pending", {}).pop(int(slot), None)
 
     def forward_host_submit(self, pcm, lengths=None, offsets=None, t_max: Optional[int] = None, seed: int = 0,
                             first_utterance_id: int = 0, out=None, kernel: str = "auto", slot: int = 0):

@@ -109,6 +109,13 @@ def test_assemble_batch_policies(bat):
     # slice: frames beyond max_audio_length are never computed; n_frames is clipped
     sl = bat.assemble_batch(fe, d, lens, seed=43, max_over_policy="slice", max_audio_length=150, max_token_length=9)
     assert sl["features"].shape == (4, 150, 80, 3) and sl["n_frames"].tolist() == [150, 99, 150, 49]
+    # slice below a larger audio_pad_length: [B, audio_pad_length, ...] with zeros behind the slice
+    # (the reference slices per example, data.py:345-354, then padded_batch pads, run/train.py:182-197)
+    sp = bat.assemble_batch(fe, d, lens, seed=43, max_over_policy="slice", max_audio_length=150, max_token_length=9,
+                            audio_pad_length=320, mask_layers=([3, 3], [2, 2]))
+    assert sp["features"].shape == (4, 320, 80, 3) and sp["n_frames"].tolist() == [150, 99, 150, 49]
+    assert torch.equal(sp["features"][:, :150], sl["features"]) and not sp["features"][:, 150:].any()
+    assert np.array_equal(sp["mask"].cpu().numpy(), P.las_audio_mask(sp["features"].cpu().numpy(), 3, 2))
     # filter: keep-mask over n_frames and token lengths (data.py:337)
     fl = bat.assemble_batch(fe, d, lens, seed=43, max_over_policy="filter", max_audio_length=198, max_token_length=9,
                             token_lengths=torch.tensor([1, 1, 10, 9]), audio_pad_length=320)

@@ -448,8 +448,9 @@ def test_forward_host_matches_device_path(fe_mod, kernel):
     batch = np.zeros((19, L), np.int16)
     for i, n in enumerate(lengths):
         batch[i, :n] = noise_int16(n, 100 + i)
+    # (T = 70 < 74 frames of the shortest utterance: no draw can hit TF's maxval <= minval case)
     fe = fe_mod.FeatureFrontend("log-mel-spectrogram", **LIBRI, use_delta_accelerate=True,
-                                spec_augment=dict(enable=True, F=27, m_F=2, T=100, p=1.0, m_T=2))
+                                spec_augment=dict(enable=True, F=27, m_F=2, T=70, p=1.0, m_T=2))
     want, nf = fe(dev(batch), lengths=lengths, seed=43, first_utterance_id=11, kernel=kernel)
     got, nf_h = fe.forward_host(batch, lengths=lengths, seed=43, first_utterance_id=11, kernel=kernel)
     assert np.array_equal(got, want.cpu().numpy()) and np.array_equal(nf_h, nf.cpu().numpy())
@@ -458,6 +459,44 @@ def test_forward_host_matches_device_path(fe_mod, kernel):
     flat = torch.from_numpy(np.concatenate([batch[i, :n] for i, n in enumerate(lengths)])).pin_memory()
     got2, _ = fe.forward_host(flat, lengths=lengths, offsets=offsets, seed=43, first_utterance_id=11, kernel=kernel)
     assert np.array_equal(got2, got)
+
+
+@pytest.mark.parametrize("kernel", KERNELS)
+def test_invalid_draws_raise_on_the_host_path(fe_mod, kernel):
+    """tf.random.uniform raises when maxval <= minval (data.py:284-285, 297).  The fused device call
+    reports it in the status word (asynchronous); the host-buffer call reads the word back with the
+    results and raises like the reference, after delivering the (unmasked) output."""
+    sa = dict(enable=True, F=27, m_F=2, T=100, p=1.0, m_T=2)
+    fe = fe_mod.FeatureFrontend("log-mel-spectrogram", **LIBRI, spec_augment=sa)
+    lengths = [32000, 100, 16000]                      # utterance 1 has no frames: the time-mask draw is invalid
+    batch = np.zeros((3, 32000), np.int16)
+    for i, n in enumerate(lengths):
+        batch[i, :n] = noise_int16(n, 200 + i)
+    out, nf, status = fe(dev(batch), lengths=lengths, seed=43, kernel=kernel, return_status=True)
+    assert int(status.item()) & 1
+    host_out = np.full((3, 199, 80, 1), 7.0, np.float32)
+    with pytest.raises(ValueError, match="maxval <= minval"):
+        fe.forward_host(batch, lengths=lengths, seed=43, kernel=kernel, out=host_out)
+    assert np.array_equal(host_out, out.cpu().numpy())   # the results were delivered before the error
+    ok = [32000, 31000, 16000]
+    fe.forward_host(batch, lengths=ok, seed=43, kernel=kernel)   # the next step on the slot is clean
+
+
+def test_handles_do_not_lower_each_others_shared_memory_cap(fe_mod):
+    """cudaFuncAttributeMaxDynamicSharedMemorySize is per (function, device): a handle created later with
+    a smaller tile must not break an earlier handle's launches."""
+    pcm = noise_int16(20000, 8)
+    big = fe_mod.FeatureFrontend("spectrogram", 16000, 320, 160, 320)
+    a0, _ = big(dev(pcm[None]), kernel="generic")
+    small = fe_mod.FeatureFrontend("log-mel-spectrogram", 16000, 128, 64, 128, 20, None, 80.0, 7600.0)
+    small(dev(pcm[None]), kernel="generic")
+    mf = fe_mod.FeatureFrontend("mfcc", **dict(LIBRI, num_mfcc=40), use_delta_accelerate=True)
+    m0, _ = mf(dev(pcm[None]))
+    fe_mod.FeatureFrontend("mfcc", **dict(LIBRI, num_mfcc=13))(dev(pcm[None]))
+    a1, _ = big(dev(pcm[None]), kernel="generic")
+    m1, _ = mf(dev(pcm[None]))
+    torch.cuda.synchronize()
+    assert torch.equal(a0, a1) and torch.equal(m0, m1)
 
 
 def test_errors_match_reference_stack(fe_mod):
