@@ -54,25 +54,47 @@ def test_frame_count_edges():
 
 
 def test_stft_matches_torch():
+    """torch.stft as the independent implementation for EVERY case, not only fl == n: TF left-aligns the
+    window inside fft_length (zero-padding at the end) - emulated by a length-n window whose tail is
+    zero - and crops to the first n windowed samples when fl > n (a length-n head of the window)."""
     torch = pytest.importorskip("torch")
     x = noise_int16(16000, 3).astype(np.float64) / 32768.0
-    for fl, fs, n in [(320, 160, 320), (128, 64, 256), (400, 160, 512), (512, 512, 256), (127, 50, 128)]:
+    for fl, fs, n in [(320, 160, 320), (128, 64, 256), (400, 160, 512), (512, 512, 256), (127, 50, 128),
+                      (1024, 1024, 1024), (128, 80, 128)]:
         S = O.stft(x, fl, fs, n, np.float64)
-        win = torch.hann_window(fl, periodic=True, dtype=torch.float64)
-        if fl % 2 == 1:  # TF's odd-length rule: symmetric-over-(Lw-1)... emulate directly
+        if fl % 2 == 1:  # TF's odd-length rule (divide by Lw - 1): no torch equivalent, pinned in test_hann_window_rules
             win = torch.tensor(O.hann_window(fl, np.float64))
-        if fl <= n:
-            St = torch.stft(torch.tensor(x), n, fs, fl, window=win, center=False, return_complex=True)
-            # torch centres the window inside n_fft; TF left-aligns: compare via explicit frames instead
-            idx = np.arange(S.shape[0])[:, None] * fs + np.arange(fl)[None]
-            ref = np.fft.rfft(x[idx] * win.numpy()[None], n=n, axis=-1)
-            assert np.abs(S - ref).max() < 1e-12
-            if fl == n:
-                assert np.abs(S - St.T.numpy()).max() < 1e-12
-        else:  # crop to the first n windowed samples
-            idx = np.arange(S.shape[0])[:, None] * fs + np.arange(n)[None]
-            ref = np.fft.rfft(x[idx] * win.numpy()[None, :n], axis=-1)
-            assert np.abs(S - ref).max() < 1e-12
+        else:
+            win = torch.hann_window(fl, periodic=True, dtype=torch.float64)
+        full = torch.zeros(n, dtype=torch.float64)
+        full[:min(fl, n)] = win[:min(fl, n)]
+        # (fl < n: the last TF frames reach n - fl samples past the signal - under the window's zero tail)
+        xp = np.concatenate([x, np.zeros(max(n - fl, 0))])
+        St = torch.stft(torch.tensor(xp), n, fs, n, window=full, center=False, return_complex=True).T.numpy()
+        T = O.frame_count(len(x), fl, fs)        # TF counts frames with frame_length, torch with n_fft
+        assert S.shape == (T, n // 2 + 1) and St.shape[0] >= T
+        assert np.abs(S - St[:T]).max() < 1e-12, (fl, fs, n)
+
+
+@pytest.mark.parametrize("m,n,sr,lo,hi", [(80, 320, 16000, 80.0, 7600.0), (80, 1024, 22050, 10.0, 10000.0),
+                                          (123, 256, 16000, 12.0, 88.0), (40, 512, 16000, 0.0, 8000.0)])
+def test_mel_matrix_matches_kaldi_banks(m, n, sr, lo, hi):
+    """Independent filterbank: torchaudio.compliance.kaldi.get_mel_banks is linear-in-mel HTK
+    (1127 ln(1 + f/700)) like tf.signal.linear_to_mel_weight_matrix; it returns [m, n/2] (no Nyquist
+    row).  TF zeroes the DC row by construction; Kaldi's DC weight is zero whenever lo > 0."""
+    kaldi = pytest.importorskip("torchaudio.compliance.kaldi")
+    banks, _ = kaldi.get_mel_banks(m, n, float(sr), lo, hi, 100.0, -500.0, 1.0)
+    K = banks.numpy().T.astype(np.float64)                     # [n/2, m]
+    W = O.linear_to_mel_weight_matrix(m, n // 2 + 1, sr, lo, hi, dtype=np.float64)
+    first = 1 if lo == 0.0 else 0                              # (lo = 0: Kaldi keeps a DC weight, TF forces 0)
+    # torchaudio computes in float32: 7.8e-6 on the shipped set, up to 2.5e-5 where the filters are a
+    # fraction of a mel wide (123 filters between 12 and 88 Hz) and the rounding of the edges is amplified
+    assert np.abs(W[first:n // 2] - K[first:]).max() < (1e-5 if m == 80 and n == 320 else 5e-5)
+    assert np.array_equal(W[first:n // 2] > 0, K[first:] > 0) or np.abs(W[first:n // 2] - K[first:])[(W[first:n // 2] > 0) != (K[first:] > 0)].max() < 5e-5
+    if hi <= sr / 2 * (1 - 2.0 / n):
+        assert np.all(W[n // 2] == 0)                          # Nyquist row
+    W32 = O.linear_to_mel_weight_matrix(m, n // 2 + 1, sr, lo, hi)
+    assert np.abs(W32[first:n // 2] - K[first:]).max() < 6e-5
 
 
 def test_impulse_known_answer():

@@ -174,18 +174,26 @@ def test_spectrogram_grid(fe_mod, fl, fs, n):
 
 @pytest.mark.parametrize("sr,fl,fs,n,m,c,lo,hi", REF_MFCC_GRID + [(16000, 320, 160, 320, 80, 40, 80.0, 7600.0)])
 def test_mfcc_grid(fe_mod, sr, fl, fs, n, m, c, lo, hi):
+    """make_mfcc (data.py:192-241) over the reference's grid (tests/test_data.py:114-122), as two tight
+    statements instead of one loose one: (i) the log-mel the coefficients are made of holds the stated
+    log-mel tolerance against the float64 oracle (linear-domain rule below the floor - the rows with
+    empty or nearly empty filters, M = 123 / 321 / 333); (ii) the coefficients are the oracle's
+    float64 DCT-II * (2M)^-1/2 of THAT log-mel, up to float32 rounding of an M-term sum."""
     pcm = noise_int16(20000, 9)
+    x64 = pcm.astype(np.float64) / 32768.0
     fn = fe_mod.make_mfcc(sr, fl, fs, n, m, c, float(lo), float(hi))
     got = fn(pcm.astype(np.float32) / 32768.0).cpu().numpy()
-    want = O.make_mfcc(pcm.astype(np.float64) / 32768.0, sr, fl, fs, n, m, c, lo, hi, dtype=np.float64)
+    want = O.make_mfcc(x64, sr, fl, fs, n, m, c, lo, hi, dtype=np.float64)
     assert got.shape == want.shape == ((20000 - fl + fs) // fs, c, 1)
-    # MFCC = orthogonal-ish mix of log-mels: |dct row|_1 <= 2M/sqrt(2M); bound the error accordingly
-    logmel = O.make_log_mel_spectrogram(pcm.astype(np.float64) / 32768.0, sr, fl, fs, n, m, lo, hi, dtype=np.float64)
-    if (np.exp(logmel) - 1e-12 >= 1e-7).all():
+    lm_fn = fe_mod.make_log_mel_spectrogram(sr, fl, fs, n, m, float(lo), float(hi))
+    lm = lm_fn(pcm.astype(np.float32) / 32768.0).cpu().numpy()
+    lm_want = O.make_log_mel_spectrogram(x64, sr, fl, fs, n, m, lo, hi, dtype=np.float64)
+    assert_logmel_close(lm, lm_want, what="mfcc grid log-mel %s" % ((sr, fl, fs, n, m),))           # (i)
+    dct_of_own = lm[..., 0].astype(np.float64) @ O.dct2_matrix(m, c)                                   # (ii)
+    bound = 8.0 * m * 2.0 ** -24 * np.abs(lm).max() * 2.0 / np.sqrt(2.0 * m)
+    assert np.abs(got[..., 0] - dct_of_own).max() <= bound, (np.abs(got[..., 0] - dct_of_own).max(), bound)
+    if (np.exp(lm_want) - 1e-12 >= 1e-7).all():   # every bin above the floor: the direct bound follows from (i)
         assert np.abs(got - want).max() <= 1e-3 * np.sqrt(2.0 * m)
-    else:   # bins at the floor amplify rounding in the log: compare with a float32-scale bound
-        assert np.abs(got - want).max() <= 0.25 * np.sqrt(2.0 * m)
-        assert np.median(np.abs(got - want)) <= 1e-2
 
 
 # ----------------------------------------------------------------------------------------------
