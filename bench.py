@@ -68,13 +68,19 @@ def ncu_traffic():
 
 
 class ClockSampler:
-    """Samples SM clock + throttle reasons through NVML while the timed region runs."""
+    """Samples SM clock + throttle reasons through NVML.  The thread is started BEFORE the warm-up steps
+    (NVML initialisation and thread start-up take milliseconds: between the warm-up and the timed region
+    they would leave the GPU idle long enough to drop its clocks, which a 2 ms timed region then pays
+    for); `mark()` / `stop()` bracket the timed region and only samples taken inside it are reported."""
+
+    PERIOD_S = 0.0005
 
     def __init__(self, index):
-        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self.samples, self.max_mhz = [], None      # (time, sm_mhz, reason mask)
         self._stop = threading.Event()
         self._thread = None
         self.index = index
+        self.t0 = self.t1 = None
         try:
             import pynvml
             pynvml.nvmlInit()
@@ -86,38 +92,48 @@ class ClockSampler:
 
     def _loop(self):
         nv = self.nv
-        names = {
-            getattr(nv, "nvmlClocksEventReasonHwSlowdown", 0x8): "hw_slowdown",
-            getattr(nv, "nvmlClocksEventReasonHwThermalSlowdown", 0x40): "hw_thermal_slowdown",
-            getattr(nv, "nvmlClocksEventReasonSwThermalSlowdown", 0x20): "sw_thermal_slowdown",
-            getattr(nv, "nvmlClocksEventReasonSwPowerCap", 0x4): "sw_power_cap",
-        }
         while not self._stop.is_set():
             try:
-                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                mhz = nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)
                 try:
                     mask = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
                 except Exception:
                     mask = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
-                for bit, name in names.items():
-                    if mask & bit:
-                        self.reasons.add(name)
+                self.samples.append((time.perf_counter(), mhz, mask))
             except Exception:
                 pass
-            time.sleep(0.002)
+            time.sleep(self.PERIOD_S)
 
     def start(self):
         if self.nv is not None and not os.environ.get("B200MEL_BENCH_NO_SAMPLER"):
             self._thread = threading.Thread(target=self._loop, daemon=True)
             self._thread.start()
 
+    def mark(self):
+        self.t0 = time.perf_counter()
+
     def stop(self):
+        self.t1 = time.perf_counter()
         self._stop.set()
         if self._thread is not None:
             self._thread.join()
-        med = float(np.median(self.samples)) if self.samples else None
-        return {"sm_mhz": med, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
-                "samples": len(self.samples)}
+        nv = self.nv
+        names = {} if nv is None else {
+            getattr(nv, "nvmlClocksEventReasonHwSlowdown", 0x8): "hw_slowdown",
+            getattr(nv, "nvmlClocksEventReasonHwThermalSlowdown", 0x40): "hw_thermal_slowdown",
+            getattr(nv, "nvmlClocksEventReasonSwThermalSlowdown", 0x20): "sw_thermal_slowdown",
+            getattr(nv, "nvmlClocksEventReasonSwPowerCap", 0x4): "sw_power_cap",
+        }
+        inside = [s for s in self.samples if self.t0 is not None and self.t0 <= s[0] <= self.t1]
+        if not inside and self.samples and self.t0 is not None:   # (region shorter than one period: the nearest sample)
+            inside = [min(self.samples, key=lambda s: abs(s[0] - 0.5 * (self.t0 + self.t1)))]
+        reasons = set()
+        for _, _, mask in inside:
+            for bit, name in names.items():
+                if mask & bit:
+                    reasons.add(name)
+        med = float(np.median([s[1] for s in inside])) if inside else None
+        return {"sm_mhz": med, "sm_max_mhz": self.max_mhz, "reasons": sorted(reasons), "samples": len(inside)}
 
 
 _JSON_FD = []  # the real stdout, saved while fd 1 points at stderr (multi-rank runs)
@@ -221,24 +237,38 @@ def main():
     ring_out = [torch.empty((B, T, 80, 1), dtype=torch.float32, device=dev) for _ in range(RING)]
     stream = torch.cuda.current_stream(dev)
     d_lengths = torch.full((B,), L, dtype=torch.int32, device=dev)   # resident: no per-step H2D
+    d_nframes = torch.empty((B,), dtype=torch.int32, device=dev)
 
     def step(i):
-        fe(ring_in[i % RING], lengths=d_lengths, out=ring_out[i % RING], kernel=args.kernel)
+        fe(ring_in[i % RING], lengths=d_lengths, out=ring_out[i % RING], n_frames=d_nframes, kernel=args.kernel)
 
-    for i in range(warmup):
-        step(i)
+    # staging: every ring slot goes through the path once (first touch of the output pages, the kernel's
+    # status word checked on real data) before the W warm-up steps
+    status = torch.zeros((1,), dtype=torch.int32, device=dev)
+    for i in range(RING):
+        _, _, st_i = fe(ring_in[i], lengths=d_lengths, out=ring_out[i], kernel=args.kernel, return_status=True)
+        status |= st_i
     torch.cuda.synchronize()
+    if int(status.item()) != 0:
+        raise SystemExit("bench.py: kernel status word %#x on the staged batches (0x100 = pipeline wait timed out)" % int(status.item()))
     sampler = ClockSampler(torch.cuda._get_nvml_device_index(dev) if hasattr(torch.cuda, "_get_nvml_device_index")
                            else local_rank)
-    launches0 = fe.launch_count
+    sampler.start()
+    launches0 = None
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    for i in range(warmup):
+        step(i)
+    launches0 = fe.launch_count
+    # nothing but the barrier + synchronize stands between the warm-up steps and the timed region
     if dist is not None:
         dist.barrier()
     torch.cuda.synchronize()
-    sampler.start()
+    sampler.mark()
     ev0.record(stream)
+    t_host0 = time.perf_counter()
     for i in range(args.steps):
         step(i)
+    host_us_per_call = (time.perf_counter() - t_host0) * 1e6 / max(args.steps, 1)   # enqueue cost, GPU running behind
     ev1.record(stream)
     torch.cuda.synchronize()
     if dist is not None:
@@ -322,7 +352,7 @@ def main():
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": ncu_traffic(), "peak_source": peak_src,
                      "algorithmic_bytes_per_launch": ALGO_BYTES_PER_STEP,
-                     "launch_us": per_launch_s * 1e6},
+                     "launch_us": per_launch_s * 1e6, "host_enqueue_us_per_step": host_us_per_call},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": B * L * 2, "d2h_bytes_per_step": B * T * 80 * 4,
                 "steps": e2e_steps,
                 "timer": "host wall clock around the loop of C-ABI calls, max over ranks",

@@ -41,6 +41,18 @@ int cuda_fail(cudaError_t e, const char* what) {
     if (_e != cudaSuccess) return cuda_fail(_e, #expr);  \
   } while (0)
 
+// Raise a kernel's dynamic shared-memory cap to the device maximum (opt-in limit minus the kernel's
+// static shared memory).  The attribute belongs to the (function, device) pair, not to a handle: setting
+// it to one handle's own tile size would lower the cap under every earlier handle on the device.
+template <typename K>
+cudaError_t raise_smem_cap(K kernel, int max_smem_optin) {
+  cudaFuncAttributes fa;
+  cudaError_t e = cudaFuncGetAttributes(&fa, kernel);
+  if (e != cudaSuccess) return e;
+  const int cap = max_smem_optin - static_cast<int>(fa.sharedSizeBytes);
+  return cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, cap > 0 ? cap : 0);
+}
+
 template <typename T>
 cudaError_t upload(const std::vector<T>& v, T** dptr) {
   cudaError_t e = cudaMalloc(reinterpret_cast<void**>(dptr), v.size() * sizeof(T));
@@ -179,7 +191,7 @@ int b200mel_create(const b200mel_config* config, int device, b200mel_handle** ou
   h->g_per_warp_floats = 4 * p.Nc + ((p.cfg.audio_feature_type == B200MEL_FEATURE_MFCC) ? p.cfg.num_mel_bins : 0);
   h->g_per_warp_floats = (h->g_per_warp_floats + 3) & ~3;
   int warps = 8, ft = 64;
-  const size_t budget = static_cast<size_t>(h->max_smem_optin > 0 ? h->max_smem_optin : 48 * 1024) - 1024;
+  const size_t budget = static_cast<size_t>(h->max_smem_optin > 0 ? h->max_smem_optin : 48 * 1024) - 2048;
   auto smem_need = [&](int w, int f) {
     return (static_cast<size_t>(w) * h->g_per_warp_floats + static_cast<size_t>(f + h->g_halo) * p.F) * sizeof(float);
   };
@@ -193,10 +205,7 @@ int b200mel_create(const b200mel_config* config, int device, b200mel_handle** ou
   h->g_warps = warps;
   h->g_ft = ft;
   h->g_smem = smem_need(warps, ft);
-  // The attribute belongs to the (function, device) pair, not to the handle: a later handle with a
-  // smaller tile would lower the cap under an earlier one.  Always raise it to the device maximum.
-  e = cudaFuncSetAttribute(generic_frontend_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                           h->max_smem_optin > 0 ? h->max_smem_optin : static_cast<int>(h->g_smem));
+  e = raise_smem_cap(generic_frontend_kernel, h->max_smem_optin);
   if (e != cudaSuccess) {
     b200mel_destroy(h);
     return cuda_fail(e, "cudaFuncSetAttribute(generic_frontend_kernel)");
@@ -245,8 +254,8 @@ int b200mel_create(const b200mel_config* config, int device, b200mel_handle** ou
   }
   if (h->tc_ok && p.cfg.audio_feature_type == B200MEL_FEATURE_MFCC) {
     const size_t smem = mfcc_post_smem_bytes(p.cfg.num_mel_bins, p.n_mfcc_eff);
-    if (p.cfg.num_mel_bins > kMfccMaxM || p.n_mfcc_eff > kMfccMaxC || smem > static_cast<size_t>(h->max_smem_optin) ||
-        cudaFuncSetAttribute(mfcc_post_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem_optin) != cudaSuccess) {
+    if (p.cfg.num_mel_bins > kMfccMaxM || p.n_mfcc_eff > kMfccMaxC || smem + 2048 > static_cast<size_t>(h->max_smem_optin) ||
+        raise_smem_cap(mfcc_post_kernel, h->max_smem_optin) != cudaSuccess) {
       cudaGetLastError();
       h->tc_ok = false;
     }

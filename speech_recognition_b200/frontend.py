@@ -76,6 +76,7 @@ class FeatureFrontend:
         self._cfg = cfg
         self._handle = ctypes.c_void_p()
         lib = _lib.load()
+        self._forward = lib.b200mel_forward
         _lib.check(lib.b200mel_create(ctypes.byref(cfg), dev.index, ctypes.byref(self._handle)))
         f, c, n = ctypes.c_int32(), ctypes.c_int32(), ctypes.c_int32()
         _lib.check(lib.b200mel_feature_shape(self._handle, ctypes.byref(f), ctypes.byref(c), ctypes.byref(n)))
@@ -130,11 +131,14 @@ class FeatureFrontend:
     def __call__(self, pcm: torch.Tensor, lengths=None, offsets=None, t_max: Optional[int] = None,
                  seed: int = 0, first_utterance_id: int = 0, mask_table: Optional[torch.Tensor] = None,
                  out: Optional[torch.Tensor] = None, kernel: str = "auto", return_status: bool = False,
-                 validate: bool = False) -> Tuple[torch.Tensor, torch.Tensor]:
+                 validate: bool = False, n_frames: Optional[torch.Tensor] = None
+                 ) -> Tuple[torch.Tensor, torch.Tensor]:
         """pcm: CUDA int16 or float32; dense [B, L] (``lengths`` optional) or ragged 1-D with
         ``offsets`` [B] (int64, element offsets) and ``lengths`` [B].  Returns
         (features [B, t_max, F, C] float32, n_frames [B] int32), both on the device; padding
-        frames are exactly +0.0.  Asynchronous on the current torch stream.
+        frames are exactly +0.0.  Asynchronous on the current torch stream (usual torch rules: tensors
+        allocated on another stream are the caller's to synchronise).  ``out`` / ``n_frames`` may be
+        passed to reuse buffers (a steady-state caller then allocates nothing per step).
 
         Preconditions.  Host-side ``lengths`` / ``offsets`` are range-checked here.  Device-side ones
         are NOT looked at (that would be a stream synchronisation per call): the caller guarantees
@@ -211,7 +215,11 @@ class FeatureFrontend:
             if out.shape != (B, t_max, F, C) or out.dtype != torch.float32 or not out.is_contiguous() \
                     or out.device != self.device:
                 raise ValueError("out must be a contiguous float32 [B, t_max, F, C] tensor on %s" % self.device)
-        n_frames = torch.empty((B,), dtype=torch.int32, device=self.device)
+        if n_frames is None:
+            n_frames = torch.empty((B,), dtype=torch.int32, device=self.device)
+        elif n_frames.shape != (B,) or n_frames.dtype != torch.int32 or not n_frames.is_contiguous() \
+                or n_frames.device != self.device:
+            raise ValueError("n_frames must be a contiguous int32 [B] tensor on %s" % self.device)
         status = torch.zeros((1,), dtype=torch.int32, device=self.device) if return_status else None
         if mask_table is not None:
             n = 2 * (self.num_freq_masks + self.num_time_masks)
@@ -221,14 +229,12 @@ class FeatureFrontend:
         if kernel not in _lib.KERNELS:
             raise ValueError("kernel must be one of %s" % sorted(_lib.KERNELS))
         stream = torch.cuda.current_stream(self.device).cuda_stream
-        _lib.check(_lib.load().b200mel_forward(
+        # (temporaries made above - device copies of host lengths / offsets - were allocated on this same
+        #  stream: the caching allocator reuses them in stream order, no record_stream needed)
+        _lib.check(self._forward(
             self._handle, _ptr(pcm), dt, _ptr(d_offsets), _ptr(d_lengths), B, row_stride, _ptr(out), t_max,
             _ptr(n_frames), _ptr(mask_table), seed & 0xFFFFFFFFFFFFFFFF, first_utterance_id & 0xFFFFFFFFFFFFFFFF,
             _ptr(status), _lib.KERNELS[kernel], ctypes.c_void_p(stream)))
-        # keep inputs alive until the stream has consumed them
-        for t in (pcm, d_lengths, d_offsets, mask_table):
-            if t is not None:
-                t.record_stream(torch.cuda.current_stream(self.device))
         if return_status:
             return out, n_frames, status
         return out, n_frames
