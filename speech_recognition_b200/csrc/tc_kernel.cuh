@@ -20,11 +20,12 @@
 //   * the radix-5 stage over r, power, sparse mel (FFMA immediates), log and the SpecAugment /
 //     delta / padding epilogue run on the CUDA cores, one thread per frame, straight from TMEM.
 //
-// Roles (512 threads, one persistent CTA per SM, tiles of 128 frames): warp 0 MMA issuer, warps 1-7
-// producers (PCM -> exact f16 hi/lo streams), warps 8-15 two epilogue groups (thread = frame = TMEM
-// lane, each group reduces half of the accumulator columns).  TMEM is used as a ring of eight
-// 64-column accumulator slots (a tile needs five); shared memory holds B (80 KB), one A stage (85 KB)
-// and the output staging tile (42 KB).  DESIGN.md section 4.1 has the pipeline and the measurements.
+// Roles (640 threads, one persistent CTA per SM, tiles of 128 frames): warp 0 MMA issuer, warps 1-7
+// producers (PCM -> exact f16 hi/lo streams), warps 8-19 three epilogue groups (thread = frame = TMEM
+// lane, each group reduces a third of the accumulator columns).  TMEM is used as a ring of eight
+// 64-column accumulator slots (a tile needs five); shared memory holds B (80 KB), one A stage (85 KB),
+// the output staging tile (42 KB) and the epilogue groups' hand-over zone (10 KB).  DESIGN.md section
+// 4.1 has the pipeline and the measurements.
 #pragma once
 
 #include <cuda.h>
@@ -35,7 +36,10 @@
 #include "common.cuh"
 #include "plan.h"
 #include "tc_ptx.cuh"
-#include "tc_tables_generated.inc"
+#ifndef TC_TABLES_INC
+#define TC_TABLES_INC "tc_tables_generated.inc"   // (variant builds: another column split of the epilogue groups)
+#endif
+#include TC_TABLES_INC
 
 namespace b200mel {
 
@@ -46,21 +50,39 @@ constexpr int kTcSmemB = 0;
 constexpr int kTcSmemA = 10 * kTcBBytes;                       // 81920
 constexpr int kTcSmemOut = kTcSmemA + 10 * kTcStreamBytes;     // 168960
 constexpr int kTcOutPitch = 84;                                // floats per staged row (16-B aligned, conflict-free)
-constexpr int kTcSmemCtl = kTcSmemOut + kTcTileM * kTcOutPitch * 4;  // 211968
+// hand-over zone of the three epilogue groups: TC_PARK_PITCH floats per row (partial sums of the mel bins
+// two groups feed, finished values on their way to the group that stores their float4 group)
+constexpr int kTcSmemPark = kTcSmemOut + kTcTileM * kTcOutPitch * 4;  // 211968
+constexpr int kTcSmemCtl = kTcSmemPark + kTcTileM * TC_PARK_PITCH * 4;
 constexpr int kTcSmemMask = kTcSmemCtl + 256;                  // SpecAugment tables of the CTA's tiles
-constexpr int kTcMaskTiles = 128;                              // ... at most this many tiles per CTA
+constexpr int kTcMaskTiles = 64;                               // ... at most this many tiles per CTA
 constexpr int kTcMaskEntries = 16;                             // ... and 8 masks (start, width) per utterance
 constexpr int kTcSmemWalk = kTcSmemMask + kTcMaskTiles * kTcMaskEntries * 4;  // one work cursor per warp (16 x 32 B)
 constexpr int kTcSmemList = kTcSmemWalk + 512;                 // the CTA's tiles: (utterance, tile, length, block offset)
-constexpr int kTcListTiles = 512;                              // ... at most this many per CTA and launch
+constexpr int kTcListTiles = 256;                              // ... at most this many per CTA and launch
 constexpr int kTcSmemTotal = kTcSmemList + kTcListTiles * 16 + 1024;  // + alignment slack
-// Four warpgroups: MMA issuer (warp 0) + producers (warps 1-7), epilogue groups A and B (warps 8-11,
-// 12-15).  The launch allocates 128 registers per thread; setmaxnreg moves the producers' spare
-// registers to the epilogue (per SM sub-partition: 2 x 96 + 2 x 160 = 512).
-constexpr int kTcThreads = 512;
+static_assert(kTcSmemTotal <= 232448, "shared memory budget (227 KB per CTA)");
+// Warps: 0 = MMA issuer, 1-7 = producers (224 threads), 8-19 = epilogue groups A, B, C (3 x 4 warps,
+// warp % 4 = TMEM lane quadrant).  20 warps on purpose: registers are allocated to a CTA in units of four
+// warps, so 21 warps would be charged as 24 (80 registers per thread at launch instead of 96).  The launch
+// allocates 96 registers per thread (640 x 96 = 60 K of the 64 K) and every role fits: each epilogue group
+// keeps only the ~34 mel accumulators its own FFT bins feed (ptxas: no spills), the producers hold two
+// groups of raw words.  TC_REGS_E / TC_REGS_P (variant builds) move registers between the roles with
+// setmaxnreg, within 8 x 32 x P + 12 x 32 x E <= 61 440.
+#ifndef TC_REGS_E
+#define TC_REGS_E 96
+#endif
+#ifndef TC_REGS_P
+#define TC_REGS_P 96
+#endif
+constexpr int kTcThreads = 640;
+constexpr int kTcLaunchRegs = 96;
 constexpr int kTcMmaWarp = 0;
 constexpr int kTcProducerThreads = 224;
-constexpr int kTcRegsEpilogue = 160, kTcRegsProducer = 96;
+constexpr int kTcEpilogueThreads = 384;
+constexpr int kTcRegsEpilogue = TC_REGS_E, kTcRegsProducer = TC_REGS_P;
+static_assert(8 * 32 * kTcRegsProducer + 12 * 32 * kTcRegsEpilogue <= kTcThreads * kTcLaunchRegs, "register pool");
+static_assert(kTcRegsProducer <= kTcLaunchRegs && kTcRegsEpilogue >= kTcLaunchRegs, "setmaxnreg direction");
 constexpr int kTcBScaleLog2 = 10;          // B is stored as 2^10 * w * twiddle
 // power = |Y|^2 * 2^(-2*10) (B scale) * 2^(-30) (int16 -> [-1, 1) twice)
 #define TC_PSCALE 0x1p-50f
@@ -90,8 +112,9 @@ inline bool tc_plan_matches(const HostPlan& p) {
 // Host: build the B operand (window x twiddle, two f16 terms) directly in its swizzled shared-memory
 // layout: matrix (term, r) at (term*5 + r) * 8 KB; row n (output column) = 128 B of K = 64 f16;
 // SWIZZLE_128B: 16-byte chunk index ^= (row & 7).
-//   column 0: k1 = 0 (real);  column 1: the k1 = 32 term, sum_j (-1)^j s w (real, phase e^{-i pi r/5}
-//   applied in the epilogue);  columns 2 k1, 2 k1 + 1: Re / Im of w W320^{(5j+r) k1}, k1 = 1..31.
+//   Column order = kTcColKind / kTcColK1 (generated, see gen_tc_tables.cc): quad 0 = Re, Im of k1 = 1,
+//   k1 = 0 (real), the k1 = 32 term sum_j (-1)^j s w (real; its phase e^{-i pi r/5} is applied in the
+//   epilogue); quad q = Re k1 = 2q, Re k1 = 2q + 1, Im k1 = 2q, Im k1 = 2q + 1 ("planar pairs").
 inline bool tc_plan_build(const HostPlan& p, TcPlan& tc, int max_smem_optin) {
   if (!tc_plan_matches(p) || max_smem_optin < kTcSmemTotal) return false;
   std::vector<__half> img(10 * kTcBBytes / 2);
@@ -102,12 +125,12 @@ inline bool tc_plan_build(const HostPlan& p, TcPlan& tc, int max_smem_optin) {
         const int s = 5 * j + r;
         const double w = static_cast<double>(p.window[s]);
         double f;
-        if (n == 0) f = 1.0;
-        else if (n == 1) f = (j & 1) ? -1.0 : 1.0;
+        const int kind = kTcColKind[n], k1 = kTcColK1[n];
+        if (kind == 2) f = 1.0;
+        else if (kind == 3) f = (j & 1) ? -1.0 : 1.0;
         else {
-          const int k1 = n >> 1;
           const double a = -2.0 * M_PI * static_cast<double>((s * k1) % 320) / 320.0;
-          f = (n & 1) ? sin(a) : cos(a);
+          f = kind == 1 ? sin(a) : cos(a);
         }
         const double v = scale * w * f;
         const __half hi = __float2half_rn(static_cast<float>(v));

@@ -5,10 +5,10 @@ namespace b200mel {
 
 struct TcCtl {
   // the A stage is handed over in two phases: [0] = streams of residues 0-2, [1] = residues 3-4
-  uint64_t a_full[2];   // producers (224 arrivals) -> MMA: the phase's streams (hi, lo) are in smem
+  uint64_t a_full[2];   // producers (256 arrivals) -> MMA: the phase's streams (hi, lo) are in smem
   uint64_t a_empty[2];  // tcgen05.commit -> producers: the MMAs that read the phase's streams are done
   uint64_t acc_full;    // tcgen05.commit -> epilogue: the 5 accumulators of this tile are complete
-  uint64_t acc_empty;   // epilogue (256 arrivals) -> MMA: this tile's TMEM slots may be overwritten
+  uint64_t acc_empty;   // epilogue (384 arrivals) -> MMA: this tile's TMEM slots may be overwritten
   uint64_t b_full;      // TMA bulk copy -> MMA: the B operand image has landed in shared memory
   uint64_t list_full;   // epilogue warps (8 arrivals) -> everybody: the CTA's tile list is complete
   uint32_t tmem_base;
@@ -44,17 +44,14 @@ __device__ __forceinline__ float tc_masked(float v, uint32_t b0, uint32_t b1, ui
   return (w & (1u << (M & 31))) ? v * 0.0f : v;
 }
 #define TC_FIN(M_, A) (kRegMask ? tc_masked<(M_)>(tc_finish(A, eps, log_eps), mb0, mb1, mb2) : tc_finish(A, eps, log_eps))
-#define TC_FINISH1(M_, A) TC_ROW_ST(out_row + (M_), TC_FIN(M_, A))
-// shared bins: group A parks its partial sum in the staged row, group B adds its own and finishes
-#define TC_PART1(M_, A) TC_ROW_ST(out_row + (M_), (A))
-#define TC_SHARED1(M_, A) TC_ROW_ST(out_row + (M_), TC_FIN(M_, (A) + out_row[M_]))
-#define TC_FINISH4(G, A, B, C, D)                                                              \
-  TC_ROW_ST(reinterpret_cast<float4*>(out_row + 4 * (G)),                                      \
-            make_float4(TC_FIN(4 * (G), A), TC_FIN(4 * (G) + 1, B), TC_FIN(4 * (G) + 2, C), TC_FIN(4 * (G) + 3, D)))
+// generated epilogue (tc_tables_generated.inc): whole float4 groups of the staged row / of the hand-over zone
+#define TC_ST4(G, A, B, C_, D) TC_ROW_ST(reinterpret_cast<float4*>(out_row + 4 * (G)), make_float4(A, B, C_, D))
+#define TC_PARK4(S, A, B, C_, D) *reinterpret_cast<float4*>(park_row + 4 * (S)) = make_float4(A, B, C_, D)
+#define TC_UNPARK4(S) *reinterpret_cast<const float4*>(park_row + 4 * (S))
 
 #if defined(TC_TRACE)
 // developer trace (experiments/trace_roles.py): clock64 stamps of CTA 0, [role][tile][event]
-__device__ long long g_tc_trace[4][32][8];
+__device__ long long g_tc_trace[5][32][8];
 #define TC_STAMP(ROLE, N, EV)                                                   \
   if (blockIdx.x == 0 && (N) < 32) g_tc_trace[ROLE][N][EV] = clock64();
 __device__ __forceinline__ long long tc_clock_fenced() {
@@ -257,7 +254,7 @@ __device__ __forceinline__ void tc_walk_step(TcWalk& w, const int32_t* __restric
   } while (w.na == 0 && w.b + 1 < batch);
 }
 
-// SpecAugment draws of this CTA's tiles, by the 256 epilogue threads while they wait for the first
+// SpecAugment draws of this CTA's tiles, by the 384 epilogue threads while they wait for the first
 // accumulators: raw Philox words first (one per thread), then one thread per tile turns them into
 // the reference's (start, width) table in draw order (common.cuh: specaug_draw_table).
 struct TcDrawArgs {
@@ -268,13 +265,13 @@ struct TcDrawArgs {
 };
 __device__ __noinline__ void tc_draw_tables(int32_t* tab, const TcDrawArgs p, const int4* list, int n_tiles, int etid) {
   const int n_e = 2 * (p.n_masks_f + p.n_masks_t);
-  for (int k = etid; k < n_tiles * kTcMaskEntries; k += 256) {
+  for (int k = etid; k < n_tiles * kTcMaskEntries; k += kTcEpilogueThreads) {
     const int i = k / kTcMaskEntries, d = k - i * kTcMaskEntries;
     if (d < n_e)
       tab[k] = static_cast<int32_t>(specaug_raw_draw(p.seed, p.first_utt + static_cast<uint64_t>(list[i].x), static_cast<uint32_t>(d)));
   }
-  tc::named_bar_sync(10, 256);
-  for (int i = etid; i < n_tiles; i += 256) {
+  tc::named_bar_sync(13, kTcEpilogueThreads);
+  for (int i = etid; i < n_tiles; i += kTcEpilogueThreads) {
     const int32_t num_time = frames_of(list[i].z, 320, 160);
     int32_t* e = tab + i * kTcMaskEntries;
     int bad = 0, o = 0;
@@ -303,7 +300,7 @@ __device__ __noinline__ void tc_draw_tables(int32_t* tab, const TcDrawArgs p, co
     }
     if (bad && p.status) atomicOr(p.status, 1);
   }
-  tc::named_bar_sync(10, 256);
+  tc::named_bar_sync(13, kTcEpilogueThreads);
 }
 
 template <int C, bool kMask>
@@ -315,6 +312,7 @@ __global__ void __launch_bounds__(kTcThreads, 1)
   uint8_t* sB = smem + kTcSmemB;
   uint8_t* sA = smem + kTcSmemA;
   float* sOut = reinterpret_cast<float*>(smem + kTcSmemOut);
+  float* sPark = reinterpret_cast<float*>(smem + kTcSmemPark);
   TcCtl* ctl = reinterpret_cast<TcCtl*>(smem + kTcSmemCtl);
 
   // warp index through a shuffle: the compiler then knows it is warp-uniform (uniform registers and
@@ -330,7 +328,7 @@ __global__ void __launch_bounds__(kTcThreads, 1)
       tc::mbar_init(&ctl->a_empty[r], 1);
     }
     tc::mbar_init(&ctl->acc_full, 1);
-    tc::mbar_init(&ctl->acc_empty, 256);
+    tc::mbar_init(&ctl->acc_empty, kTcEpilogueThreads);
     tc::mbar_init(&ctl->list_full, 8);
     tc::fence_mbar_init();
     // B operand (80 KB, constant): two bulk copies by the TMA engine, only the MMA issuer waits for
@@ -341,7 +339,7 @@ __global__ void __launch_bounds__(kTcThreads, 1)
   }
   if (warp == kTcMmaWarp) tc::tmem_alloc(&ctl->tmem_base, 512);
   const int32_t t_max32 = p.t_max < 0x7fffffff ? static_cast<int32_t>(p.t_max) : 0x7fffffff;
-  TcWalk* swk = reinterpret_cast<TcWalk*>(smem + kTcSmemWalk) + warp;  // this warp's work cursor slot
+  TcWalk* swk = reinterpret_cast<TcWalk*>(smem + kTcSmemWalk) + (warp & 15);  // (warps 0-7 use their cursor slot)
   // The CTA's tiles in processing order, (utterance, tile, length, 8-sample block offset or bit 31 =
   // "not 16-byte aligned"): built by the epilogue warps while they wait for the first accumulators,
   // read by every role (one 16-byte broadcast load per tile instead of cursor arithmetic).
@@ -384,7 +382,7 @@ __global__ void __launch_bounds__(kTcThreads, 1)
 
   if (warp >= 1 && warp < 8) {
     // ======================= PRODUCERS (warps 1-7: 224 threads) =================================
-    tc::setmaxnreg_dec<kTcRegsProducer>();
+    if (kTcRegsProducer < kTcLaunchRegs) tc::setmaxnreg_dec<kTcRegsProducer>();
     // One A stage, refilled in two phases: the streams of residues 0-2 as soon as the previous tile's
     // MMAs of those residues have completed, residues 3-4 after the rest (those MMAs wait for the
     // epilogue to release TMEM).  The raw PCM of the NEXT tile is loaded into the same registers at
@@ -392,13 +390,15 @@ __global__ void __launch_bounds__(kTcThreads, 1)
     const int ptid = tid - 32;
     uint32_t n = 0;  // active tiles processed so far by this CTA
     // 516 groups of 40 samples = 129 hops (128 frames + the half-row of overlap): groups ptid and
-    // ptid + 224 for every thread, ptid + 448 for the first 68
-    const bool third = ptid < 516 - 2 * kTcProducerThreads;
-    uint32_t ph[3];
+    // ptid + 224 for every thread, held in registers (and preloaded for the next tile); the last 68 groups
+    // go to threads 0..67, out of line and loaded on the spot (their range is in L2): the producers' register
+    // budget holds two groups of raw words, not three
+    const bool extra = ptid < 516 - 2 * kTcProducerThreads;
+    uint32_t ph[2];
 #pragma unroll
-    for (int i = 0; i < 3; ++i) ph[i] = tc_stream_offset(ptid + kTcProducerThreads * i);
+    for (int i = 0; i < 2; ++i) ph[i] = tc_stream_offset(ptid + kTcProducerThreads * i);
     const uint4* pcm16 = reinterpret_cast<const uint4*>(p.pcm);
-    uint32_t w[3][20];  // this thread's groups: raw words (two samples each), XOR-ed in place before use
+    uint32_t w[2][20];  // this thread's groups: raw words (two samples each), XOR-ed in place before use
     bool preloaded = false;
     // raw words of one tile -> w: absolute 8-sample block index, clamped into the utterance
 #define TC_LOAD_GROUP(I, BLK0, BLO, BHI)                                                               \
@@ -412,7 +412,7 @@ __global__ void __launch_bounds__(kTcThreads, 1)
   }
     if (!tc::mbar_wait(&ctl->list_full, 0)) timed_out = true;
     const int n_tiles = ctl->n_tiles;
-    // Register budget: the 60 raw words of the NEXT tile are live across the top of the loop, so
+    // Register budget: the 40 raw words of the NEXT tile are live across the top of the loop, so
     // nothing about the tiles is carried in registers - every use re-reads the list entry.
     // next tile: first block and clamp range, all in absolute 8-sample blocks (< 2^31 blocks)
 #define TC_NEXT_RANGE()                                                                           \
@@ -441,10 +441,9 @@ __global__ void __launch_bounds__(kTcThreads, 1)
           const int32_t b_0 = b_lo + 20 * (cur.y * tp.tout - tp.halo);
           TC_LOAD_GROUP(0, b_0, b_lo, b_hi)
           TC_LOAD_GROUP(1, b_0, b_lo, b_hi)
-          if (third) { TC_LOAD_GROUP(2, b_0, b_lo, b_hi) }
         }
 #pragma unroll
-        for (int i = 0; i < 3; ++i)
+        for (int i = 0; i < 2; ++i)
 #pragma unroll
           for (int k = 0; k < 20; ++k) w[i][k] ^= 0x80008000u;
         if (ptid == 0) { TC_STAMP(0, n, 1) }
@@ -457,18 +456,15 @@ __global__ void __launch_bounds__(kTcThreads, 1)
         tc_produce_res<0>(w[1], sA, ph[1]);
         tc_produce_res<1>(w[1], sA, ph[1]);
         tc_produce_res<2>(w[1], sA, ph[1]);
-        if (third) {
-          tc_produce_res<0>(w[2], sA, ph[2]);
-          tc_produce_res<1>(w[2], sA, ph[2]);
-          tc_produce_res<2>(w[2], sA, ph[2]);
+        if (extra) {
+          const int4 cur = sList[ti];
+          const int32_t b_lo = cur.w;
+          tc_produce_extra(pcm16, b_lo + 20 * (cur.y * tp.tout - tp.halo), b_lo, b_lo + (cur.z >> 3) - 1, sA,
+                           ptid + 2 * kTcProducerThreads, 0);
         }
         tc::fence_async_smem();  // generic-proxy writes -> visible to the tensor core (async proxy)
         tc::mbar_arrive(&ctl->a_full[0]);
         if (ptid == 0) { TC_STAMP(0, n, 3) }
-        if (ptid == 64) { TC_STAMP(2, n, 6) }
-        if (ptid == 128) { TC_STAMP(2, n, 7) }
-        if (ptid == 160) { TC_STAMP(3, n, 6) }
-        if (ptid == 223) { TC_STAMP(3, n, 7) }
         // ---- phase 2: residues 3-4, then reload the registers with the next tile's PCM
         if (n > 0 && !timed_out && !tc::mbar_wait(&ctl->a_empty[1], par)) timed_out = true;
         if (ptid == 0) { TC_STAMP(0, n, 4) }
@@ -476,21 +472,21 @@ __global__ void __launch_bounds__(kTcThreads, 1)
         tc_produce_res<4>(w[0], sA, ph[0]);
         tc_produce_res<3>(w[1], sA, ph[1]);
         tc_produce_res<4>(w[1], sA, ph[1]);
-        if (third) {
-          tc_produce_res<3>(w[2], sA, ph[2]);
-          tc_produce_res<4>(w[2], sA, ph[2]);
+        if (extra) {
+          const int4 cur = sList[ti];
+          const int32_t b_lo = cur.w;
+          tc_produce_extra(pcm16, b_lo + 20 * (cur.y * tp.tout - tp.halo), b_lo, b_lo + (cur.z >> 3) - 1, sA,
+                           ptid + 2 * kTcProducerThreads, 1);
         }
         tc::fence_async_smem();
         tc::mbar_arrive(&ctl->a_full[1]);
         if (ptid == 96) { TC_STAMP(0, n, 5) }
-        if (ptid == 192) { TC_STAMP(0, n, 7) }
         // the registers are free: start loading the next tile's PCM (its range is in L2 by now).
         // After the fence on purpose - the fence waits for this thread's outstanding loads.
         if (next_ok) {
           TC_NEXT_RANGE()
           TC_LOAD_GROUP(0, nb_0, nb_lo, nb_hi)
           TC_LOAD_GROUP(1, nb_0, nb_lo, nb_hi)
-          if (third) { TC_LOAD_GROUP(2, nb_0, nb_lo, nb_hi) }
         }
         preloaded = next_ok;
         if (ptid == 0) { TC_STAMP(0, n, 6) }
@@ -513,7 +509,7 @@ __global__ void __launch_bounds__(kTcThreads, 1)
     // Warp 0 on purpose: the issuing thread needs an instruction slot every few cycles to keep the
     // tensor pipe fed, and the warp schedulers favour the oldest (lowest) warp of a sub-partition -
     // as the youngest warp it was starved by the epilogue warps (96 instead of 60 cycles per MMA).
-    tc::setmaxnreg_dec<kTcRegsProducer>();
+    if (kTcRegsProducer < kTcLaunchRegs) tc::setmaxnreg_dec<kTcRegsProducer>();
     if (tc::elect_one()) {
       // the issuer only needs the NUMBER of tiles of this CTA (every tile of the list is active)
       if (!tc::mbar_wait(&ctl->list_full, 0)) timed_out = true;
@@ -568,16 +564,16 @@ __global__ void __launch_bounds__(kTcThreads, 1)
     }
     __syncwarp();
   } else {
-    // ======================= EPILOGUE (warps 8-15) ==============================================
-    // thread = frame row = TMEM lane.  Two groups share every tile: group A (warps 8-11) reduces
-    // accumulator columns 0-31 of each residue (k1 = 0, 32, 1..15), group B (warps 12-15) columns
-    // 32-63 (k1 = 16..31); warps w and w + 4 work on the same 32 rows.  Each mel bin is finished by
-    // the group that feeds it; the 13 bins fed by both are parked by A in the staged row and
-    // finished by B after the pair barrier.  B then stores the 32 rows with one TMA tensor store.
-    tc::setmaxnreg_inc<kTcRegsEpilogue>();
+    // ======================= EPILOGUE (warps 8-19) ==============================================
+    // thread = frame row = TMEM lane.  Three groups share every tile: group A (warps 8-11) reduces the
+    // accumulator quads [0, TC_SPLIT_A) of each residue, B (12-15) [TC_SPLIT_A, TC_SPLIT_B), C (16-19) the
+    // rest; warps w, w + 4, w + 8 work on the same 32 rows.  Each group has its own straight-line code and
+    // its own mel accumulators (only the bins its FFT bins feed).  Values travel down the chain A -> B -> C
+    // through the hand-over zone: partial sums of bins two groups feed, and finished values on their way to
+    // the group that stores their float4 group.  C then stores the 32 rows with one TMA tensor store.
+    if (kTcRegsEpilogue > kTcLaunchRegs) tc::setmaxnreg_inc<kTcRegsEpilogue>();
     // C == 1: masks are applied to the finished values in registers (measured 102.7 -> 96.7 us on config 3);
-    // C == 3: on the staged row before the copy-out (in registers it was 2.7 % slower there: both groups
-    // pay the bit tests and neither has slack under the copy-out barriers)
+    // C == 3: on the staged row before the copy-out
     constexpr bool kRegMask = kMask && C == 1;
     const int group = (warp - 8) >> 2, wq = warp & 3;
     const int etid = tid - 256;
@@ -586,20 +582,20 @@ __global__ void __launch_bounds__(kTcThreads, 1)
     const float eps = p.epsilon, log_eps = tp.log_eps;
     const int n_masks = p.n_masks_f + p.n_masks_t;
     float* out_row = sOut + row * kTcOutPitch;
+    float* park_row = sPark + row * TC_PARK_PITCH;
     const uint32_t sOut_s = tc::smem_u32(sOut);
     const uint32_t lane_base = static_cast<uint32_t>(wq * 32) << 16;
-    const uint32_t bar_ready = 1 + wq, bar_free = 5 + wq;  // pair barriers (64 threads)
-    bool pending = false;  // C == 1: the pair's previous TMA store may still be reading the staged rows
-    bool issuer = false;   // this thread issued it (bulk async-groups are per thread)
+    // trio barriers: "rows free" C -> A, B (96 threads); A -> B and B -> C hand-overs (64 threads)
+    const uint32_t bar_free = 1 + wq, bar_ab = 5 + wq, bar_bc = 9 + wq;
+    bool issuer = false;  // (group C) this thread issued the trio's TMA stores (bulk async-groups are per thread)
     int32_t* sMask = reinterpret_cast<int32_t*>(smem + kTcSmemMask);
     // the first epilogue warp of the grid also reports the frame counts, and flags the zero-frame
     // utterances on which the reference's time-mask draw raises
     const bool reporter = blockIdx.x == 0 && warp == 8;
-    // (the cursor lives in shared memory: the epilogue's main loop has no registers to spare)
-    {
-      // ---- the CTA's tile list, in one pass over the lengths: thread (warp e, lane l) owns utterance
-      //      256 c + 8 l + e of every chunk c of 256; a warp scan of the per-lane counts gives the
-      //      index of its first active tile, and it writes those of its tiles that fall into this
+    if (warp < 16) {
+      // ---- the CTA's tile list, in one pass over the lengths (warps 8-15): thread (warp e, lane l) owns
+      //      utterance 256 c + 8 l + e of every chunk c of 256; a warp scan of the per-lane counts gives
+      //      the index of its first active tile, and it writes those of its tiles that fall into this
       //      CTA's range.  Ready ~one L2 round trip after the kernel starts. ----
       const int ew = warp - 8;
       int32_t* nfo = reporter ? p.n_frames : nullptr;
@@ -685,15 +681,14 @@ __global__ void __launch_bounds__(kTcThreads, 1)
       const int4 cur = sList[ti];
       const int b = cur.x, j = cur.y;
       const int32_t len = cur.z;
-      // SpecAugment: lane i of every group-B warp fetches entry i of the utterance's mask table now
-      // (at most 16 masks on this path); it is consumed after the whole tile has been reduced
+      // SpecAugment: lane i fetches entry i of the utterance's mask table now (at most 16 masks on this
+      // path): C == 1 every group (masks in registers), C == 3 group C (masks on the staged row)
       int32_t mask_entry = 0;
-      if (kMask && (kRegMask || group == 1) && lane < 2 * n_masks)
+      if (kMask && (kRegMask || group == 2) && lane < 2 * n_masks)
         mask_entry = p.mask_table ? __ldg(p.mask_table + static_cast<size_t>(b) * 2 * n_masks + lane)
                                   : sMask[ti * kTcMaskEntries + lane];
       const int n_fr = frames_of(len, 320, 160);
       const int t_first = j * tp.tout;  // first OUTPUT frame of this tile; row i holds frame t_first - halo + i
-      constexpr bool active = true;  // (the range holds active tiles only)
       const int t_row = t_first - tp.halo + row;
       // this row's mask map: frequency masks [f0, f0 + f) of the utterance, everything for a row inside a
       // time mask [t0, t0 + t).  (Rows that are not real frames are zero-filled or dropped anyway.)
@@ -720,131 +715,72 @@ __global__ void __launch_bounds__(kTcThreads, 1)
         }
         if (tm) mb0 = mb1 = mb2 = 0xffffffffu;
       }
-      // C == 1: the staged rows are free once the pair's previous TMA store has read them.  Nobody
-      // writes them before the group's last chunk (all finishing work is emitted there), so the
-      // hand-shake - B waits for that read and tells A - happens there, long after the read is done.
-      bool need_free = C == 1 && pending;
-      pending = false;
-#define TC_ROWS_FREE()                                                                            \
-  if (need_free) {                                                                                \
-    if (group == 1) {                                                                             \
-      if (issuer) tc::bulk_wait_read(); /* async-groups belong to the thread that committed them */ \
-      __syncwarp();                                                                               \
-      tc::named_bar_arrive(bar_free, 64);                                                         \
-    } else {                                                                                      \
-      tc::named_bar_sync(bar_free, 64);                                                           \
+      if (lane == 0 && wq == 0) { TC_STAMP(2, n, 0) }
+      if (!timed_out && !tc::mbar_wait(&ctl->acc_full, n & 1)) timed_out = true;
+      tc::tc_fence_after();
+      if (lane == 0 && wq == 0) { TC_STAMP(2, n, 1) }
+      const uint32_t t_tile = tmem_base + lane_base;
+      // One group's pass over its quads: five TMEM loads (one per residue) of four columns, the packed
+      // radix-5 + power step, the quad's mel FFMAs (immediates, named accumulators).  The TMEM slots go
+      // back to the MMA issuer right after the group's last load; all finishing work comes after that.
+      // C == 1: the staged rows and the hand-over zone of the previous tile are free once group C's TMA
+      // store has read them and C's phase 2 is over - C says so at its first quad (`CFREE`), A and B check
+      // before their first write (`ABFREE`), long after.
+#define TC_GROUP_LOOP(G, Q0, Q1, CFREE)                                                           \
+  float P[11], d[5][4];                                                                           \
+  _Pragma("unroll 1") for (int q = (Q0); q < (Q1); ++q) {                                         \
+    _Pragma("unroll") for (int r = 0; r < 5; ++r) tc::tmem_ld4(t_tile + (((5u * n + r) & 7u) << 6) + 4 * q, d[r]); \
+    tc::tmem_ld_wait();                                                                           \
+    if (q == (Q1) - 1) {                                                                          \
+      tc::tc_fence_before();                                                                      \
+      tc::mbar_arrive(&ctl->acc_empty);                                                           \
+      if (lane == 0 && wq == 0) { TC_STAMP(2 + (G), n, 2) }                                       \
     }                                                                                             \
-    need_free = false;                                                                            \
+    if ((G) == 0 && q == 0) tc_radix5_power_special(d, P);                                        \
+    else tc_radix5_power_pair(d, P);                                                              \
+    if (q == (Q0)) { CFREE }                                                                      \
+    TC_G##G##_SWITCH(q, P);                                                                       \
   }
-      if (active) {
-        if (lane == 0 && wq == 0) { TC_STAMP(2 + group, n, 0) }
-        if (!timed_out && !tc::mbar_wait(&ctl->acc_full, n & 1)) timed_out = true;
-        tc::tc_fence_after();
-        if (lane == 0 && wq == 0) { TC_STAMP(2 + group, n, 1) }
-        TC_DECL_ACC
-        float P[20], Q[6], d[5][8];
-#if defined(TC_ABLATE_ELOAD)
-#pragma unroll
-        for (int r = 1; r < 5; ++r)
-#pragma unroll
-          for (int k = 0; k < 8; ++k) d[r][k] = __int_as_float(0x3f800000 + r * 977 + k * 131 + lane);
-#endif
-        const uint32_t t_tile = tmem_base + lane_base;
-        // one rolled loop per group over its 4 chunks of 8 accumulator columns (4 values of k1) per
-        // residue; only the mel FFMAs (immediates, named accumulators) are per-chunk code
-#if defined(TC_ABLATE_EMATH)
-#define TC_RADIX_STEP(S)                                                                          \
-  { _Pragma("unroll") for (int k2 = 0; k2 < 5; ++k2) P[5 * (S) + k2] = d[k2][2 * (S)] + d[k2][2 * (S) + 1]; }
-#else
-#define TC_RADIX_STEP(S)                                                                          \
-  {                                                                                               \
-    tc_f2 xc[5];                                                                                  \
-    _Pragma("unroll") for (int r = 0; r < 5; ++r) xc[r] = tc_pk(d[r][2 * (S)], d[r][2 * (S) + 1]); \
-    tc_radix5_power2(xc, P[5 * (S)], P[5 * (S) + 1], P[5 * (S) + 2], P[5 * (S) + 3], P[5 * (S) + 4]); \
-  }
-#endif
-#if defined(TC_ABLATE_ELOAD)
-#define TC_LOAD_ROWS 1 /* (experiment: one TMEM load per chunk instead of five) */
-#else
-#define TC_LOAD_ROWS 5
-#endif
-#define TC_LOAD_CHUNK(CH)                                                                         \
-  _Pragma("unroll") for (int r = 0; r < TC_LOAD_ROWS; ++r) tc::tmem_ld8(t_tile + (((5u * n + r) & 7u) << 6) + 8 * (CH), d[r]); \
-  tc::tmem_ld_wait();                                                                             \
-  if (((CH) & 3) == 3) {                                                                          \
-    /* this thread's TMEM reads of the tile are done: hand the slots back before the arithmetic */ \
-    tc::tc_fence_before();                                                                        \
-    tc::mbar_arrive(&ctl->acc_empty);                                                             \
-    if (lane == 0 && wq == 0) { TC_STAMP(2 + group, n, 2) }                                       \
-  }
-        // both groups run the SAME loop code (instruction-cache footprint): group A chunks 0-3, B 4-7
-        const int c0 = 4 * group;
-#pragma unroll 1
-        for (int c = c0; c < c0 + 4; ++c) {
-          TC_LOAD_CHUNK(c)
-          if (c == 0) {
-            // columns 0 / 1 hold the real k1 = 0 and k1 = 32 terms: Y_r[32] = R_r * e^{-i pi r / 5}
-            float x[5];
-#pragma unroll
-            for (int r = 0; r < 5; ++r) x[r] = d[r][0];
-            tc_radix5_power_real(x, Q[0], Q[1], Q[2]);
-            const float cr[5] = {1.0f, 0.80901699437494742410f, 0.30901699437494742410f, -0.30901699437494742410f,
-                                 -0.80901699437494742410f};
-            const float sr[5] = {0.0f, 0.58778525229247312917f, 0.95105651629515357212f, 0.95105651629515357212f,
-                                 0.58778525229247312917f};
-            float xr[5], xi[5], p3, p4;
-#pragma unroll
-            for (int r = 0; r < 5; ++r) {
-              xr[r] = d[r][1] * cr[r];
-              xi[r] = -d[r][1] * sr[r];
-            }
-            tc_radix5_power(xr, xi, Q[3], Q[4], Q[5], p3, p4);
-          } else {
-            TC_RADIX_STEP(0)
-          }
-          TC_RADIX_STEP(1)
-          TC_RADIX_STEP(2)
-          TC_RADIX_STEP(3)
-          // B announces early (its first chunk: the read has long finished), A checks late (its last
-          // chunk, the first one that writes rows): neither waits for the other in practice
-          if (c == c0 + 3 - 3 * group) { TC_ROWS_FREE() }
-          switch (c) {
-            case 0: TC_MEL_CHUNK_0(Q, P); break;
-            case 1: TC_MEL_CHUNK_1(Q, P); break;
-            case 2: TC_MEL_CHUNK_2(Q, P); break;
-            case 3: TC_MEL_CHUNK_3(Q, P); break;
-            case 4: TC_MEL_CHUNK_4(Q, P); break;
-            case 5: TC_MEL_CHUNK_5(Q, P); break;
-            case 6: TC_MEL_CHUNK_6(Q, P); break;
-            default: TC_MEL_CHUNK_7(Q, P); break;
-          }
-        }
-        if (lane == 0 && wq == 0) { TC_STAMP(2 + group, n, 3) }
-        if (group == 1) {
-          // A's finished bins and parked partial sums of this row are in shared memory
-          tc::named_bar_sync(bar_ready, 64);
-          if (lane == 0 && wq == 0) { TC_STAMP(3, n, 4) }
-          TC_MEL_SHARED_B;
-          if (kMask && !kRegMask) tc_mask_row(out_row, mask_entry, p.n_masks_f, p.n_masks_t, t_row, t_row >= 0 && t_row < n_fr);
-        }
-#undef TC_LOAD_CHUNK
-#undef TC_RADIX_STEP
-        if (group == 0) tc::named_bar_arrive(bar_ready, 64);
-        if (lane == 0 && wq == 0) { TC_STAMP(2 + group, n, 5) }
-        ++n;
+      if (group == 0) {
+        TC_G0_DECL
+        TC_GROUP_LOOP(0, 0, TC_SPLIT_A, )
+        if (C == 1) tc::named_bar_sync(bar_free, 96);
+        TC_G0_PHASE1;
+        tc::named_bar_arrive(bar_ab, 64);
+      } else if (group == 1) {
+        TC_G1_DECL
+        TC_GROUP_LOOP(1, TC_SPLIT_A, TC_SPLIT_B, )
+        if (C == 1) tc::named_bar_sync(bar_free, 96);
+        TC_G1_PHASE1;
+        tc::named_bar_sync(bar_ab, 64);
+        { TC_G1_PHASE2; }
+        tc::named_bar_arrive(bar_bc, 64);
+      } else {
+        TC_G2_DECL
+        TC_GROUP_LOOP(2, TC_SPLIT_B, 16,
+                      if (C == 1) {
+                        if (issuer) tc::bulk_wait_read(); /* async-groups belong to the thread that committed them */
+                        __syncwarp();
+                        tc::named_bar_arrive(bar_free, 96);
+                      })
+        TC_G2_PHASE1;
+        tc::named_bar_sync(bar_bc, 64);
+        { TC_G2_PHASE2; }
+        if (kMask && !kRegMask) tc_mask_row(out_row, mask_entry, p.n_masks_f, p.n_masks_t, t_row, t_row >= 0 && t_row < n_fr);
       }
-      TC_ROWS_FREE()  // (tile of padding only: keep the barrier phases paired, B zero-fills below)
-#undef TC_ROWS_FREE
+#undef TC_GROUP_LOOP
+      if (lane == 0 && wq == 0) { TC_STAMP(2, n, 3) }
+      ++n;
 
       if (C == 1) {
-        // ---- group B stores the pair's 32 staged rows with ONE TMA tensor store: the box is
+        // ---- group C stores the trio's 32 staged rows with ONE TMA tensor store: the box is
         //      [32 rows x 84 floats] (the padded staging pitch) over the [B, t_max, 80] output, so
         //      the 4 pad floats of every row and the rows >= t_max fall outside the tensor and are
         //      not written.  No CTA-wide copy-out phase. ----
-        const int wq_u = __shfl_sync(0xffffffffu, wq, 0);  // provably warp-uniform
-        const int t_warp = t_first + 32 * wq_u;
-        if (t_warp < p.t_max) {
-          if (group == 1) {
+        if (group == 2) {
+          const int wq_u = __shfl_sync(0xffffffffu, wq, 0);  // provably warp-uniform
+          const int t_warp = t_first + 32 * wq_u;
+          if (t_warp < p.t_max) {
             if (t_row >= n_fr) tc_zero_row(out_row);  // padding is +0.0 (padded_batch, train.py:192-197)
             tc::fence_async_smem();
             __syncwarp();
@@ -854,15 +790,14 @@ __global__ void __launch_bounds__(kTcThreads, 1)
               issuer = true;
             }
           }
-          pending = true;
         }
       } else {
-        tc::named_bar_sync(9, 256);  // staged (and masked) rows visible to the 8 epilogue warps
+        tc::named_bar_sync(14, kTcEpilogueThreads);  // staged (and masked) rows visible to the 12 epilogue warps
         // ---- copy-out with delta / delta-delta: staged tile -> HBM.  A work item is a PAIR of float4
         //      groups of one row (8 mel bins): its 24 outputs are 96 contiguous bytes = three whole 32-byte
         //      sectors, written with three 256-bit stores (the first version wrote 48 bytes per item with
-        //      128-bit stores: every sector arrived at L2 in two halves).  128 rows x 10 pairs = exactly
-        //      five items per thread; the next item's six shared-memory loads are issued before the current
+        //      128-bit stores: every sector arrived at L2 in two halves).  128 rows x 10 pairs = 1280 items
+        //      over 384 threads; the next item's six shared-memory loads are issued before the current
         //      item's arithmetic and stores (a shared-memory round trip costs >100 cycles while the MMAs
         //      stream their operands). ----
         float* out_b = p.out + static_cast<int64_t>(b) * p.t_max * 240;
@@ -871,10 +806,10 @@ __global__ void __launch_bounds__(kTcThreads, 1)
         float* c_dst[2];
 #define TC_CO_LOAD(S, IT)                                                                              \
   {                                                                                                    \
-    const int item = etid + 256 * (IT);                                                                \
+    const int item = etid + kTcEpilogueThreads * (IT);                                                 \
     const int i = item / 10, pr = item - 10 * i;                                                       \
     const int t = t_first - tp.halo + i;                                                               \
-    c_store[S] = i >= tp.halo && t < p.t_max;                                                          \
+    c_store[S] = item < 1280 && i >= tp.halo && t < p.t_max;                                           \
     c_dst[S] = out_b + (static_cast<int64_t>(t) * 80 + 8 * pr) * 3;                                    \
     const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);                                                 \
     _Pragma("unroll") for (int k = 0; k < 6; ++k) cx[S][k] = z4;                                       \
@@ -900,10 +835,10 @@ __global__ void __launch_bounds__(kTcThreads, 1)
     const float x2[8] = {cx[S][4].x, cx[S][4].y, cx[S][4].z, cx[S][4].w, cx[S][5].x, cx[S][5].y, cx[S][5].z, cx[S][5].w}; \
     float o[24];                                                                                       \
     _Pragma("unroll") for (int m = 0; m < 8; ++m) {                                                    \
-      const float d = x0[m] - x1[m], e = x1[m] - x2[m];                                                \
+      const float dd = x0[m] - x1[m], e = x1[m] - x2[m];                                               \
       o[3 * m] = x0[m];                                                                                \
-      o[3 * m + 1] = d;                                                                                \
-      o[3 * m + 2] = d - e;                                                                            \
+      o[3 * m + 1] = dd;                                                                               \
+      o[3 * m + 2] = dd - e;                                                                           \
     }                                                                                                  \
     tc::st_global_v8(c_dst[S], o);                                                                     \
     tc::st_global_v8(c_dst[S] + 8, o + 8);                                                             \
@@ -916,12 +851,10 @@ __global__ void __launch_bounds__(kTcThreads, 1)
         TC_CO_STORE(1)
         TC_CO_LOAD(1, 3)
         TC_CO_STORE(0)
-        TC_CO_LOAD(0, 4)
         TC_CO_STORE(1)
-        TC_CO_STORE(0)
 #undef TC_CO_LOAD
 #undef TC_CO_STORE
-        tc::named_bar_sync(9, 256);  // the staging tile may be overwritten
+        tc::named_bar_sync(14, kTcEpilogueThreads);  // the staging tile and the hand-over zone may be overwritten
       }
     }
     if (C == 1 && issuer) tc::bulk_wait_all();
