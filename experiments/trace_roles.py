@@ -13,17 +13,18 @@ for _ in range(3):
     out, nf = fe(x, kernel="tc")
 torch.cuda.synchronize()
 lib = _lib.load()
-buf = (ctypes.c_longlong * (4 * 32 * 8))()
+buf = (ctypes.c_longlong * (5 * 32 * 8))()
 lib.b200mel_debug_trace.argtypes = [ctypes.c_void_p]
 assert lib.b200mel_debug_trace(buf) == 0
-t = np.array(buf[:]).reshape(4, 32, 8)
+t = np.array(buf[:]).reshape(5, 32, 8)
 t0 = t[t > 0].min()
-names = ["P ", "M ", "EA", "EB"]
+names = ["P ", "M ", "EA", "EB", "EC"]
 ev = {0: ["start", "w0", "w1", "w2", "w3", "arr_w4", "done", "arr_w7"], 1: ["top", "afull0", "pre_accE", "accE_ok", "committed", "afull1_ok"],
-      2: ["top", "accfull", "released", "loopend", "", "done", "P1w3", "P1w5"], 3: ["top", "accfull", "released", "loopend", "ready", "done", "P1w6", "P1w7"]}
+      2: ["top", "accfull", "released", "loopend", "", "done", "", ""], 3: ["top", "accfull", "released", "loopend", "phase1", "done", "bar_ab", ""],
+      4: ["top", "accfull", "released", "loopend", "phase1", "done", "bar_bc", "stored"]}
 print("kernel: top=%d setup_done=%d dep_wait_done=%d teardown=%d" % tuple(t[1, 31, e] - t0 for e in range(4)))
 t[1, 31, :] = 0
 for n in list(range(0, 2)) + list(range(9, 12)) + list(range(20, 21)):
     print("tile", n)
-    for r in range(4):
+    for r in range(5):
         print("  ", names[r], " ".join("%s=%d" % (ev[r][e], t[r, n, e] - t0) for e in range(len(ev[r])) if ev[r][e] and t[r, n, e] > 0))

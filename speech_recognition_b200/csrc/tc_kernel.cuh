@@ -66,14 +66,14 @@ static_assert(kTcSmemTotal <= 232448, "shared memory budget (227 KB per CTA)");
 // warp % 4 = TMEM lane quadrant).  20 warps on purpose: registers are allocated to a CTA in units of four
 // warps, so 21 warps would be charged as 24 (80 registers per thread at launch instead of 96).  The launch
 // allocates 96 registers per thread (640 x 96 = 60 K of the 64 K) and every role fits: each epilogue group
-// keeps only the ~34 mel accumulators its own FFT bins feed (ptxas: no spills), the producers hold two
-// groups of raw words.  TC_REGS_E / TC_REGS_P (variant builds) move registers between the roles with
+// keeps only the ~34 mel accumulators its own FFT bins feed (ptxas: no spills), the producers hold up to
+// three groups of raw words.  TC_REGS_E / TC_REGS_P (variant builds) move registers between the roles with
 // setmaxnreg, within 8 x 32 x P + 12 x 32 x E <= 61 440.
 #ifndef TC_REGS_E
-#define TC_REGS_E 96
+#define TC_REGS_E 88
 #endif
 #ifndef TC_REGS_P
-#define TC_REGS_P 96
+#define TC_REGS_P 104
 #endif
 constexpr int kTcThreads = 640;
 constexpr int kTcLaunchRegs = 96;
@@ -82,7 +82,6 @@ constexpr int kTcProducerThreads = 224;
 constexpr int kTcEpilogueThreads = 384;
 constexpr int kTcRegsEpilogue = TC_REGS_E, kTcRegsProducer = TC_REGS_P;
 static_assert(8 * 32 * kTcRegsProducer + 12 * 32 * kTcRegsEpilogue <= kTcThreads * kTcLaunchRegs, "register pool");
-static_assert(kTcRegsProducer <= kTcLaunchRegs && kTcRegsEpilogue >= kTcLaunchRegs, "setmaxnreg direction");
 constexpr int kTcBScaleLog2 = 10;          // B is stored as 2^10 * w * twiddle
 // power = |Y|^2 * 2^(-2*10) (B scale) * 2^(-30) (int16 -> [-1, 1) twice)
 #define TC_PSCALE 0x1p-50f

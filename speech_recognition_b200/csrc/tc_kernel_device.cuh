@@ -82,28 +82,6 @@ __device__ __forceinline__ void tc_xor_words(const uint4 (&raw)[5], uint32_t (&w
   }
 }
 
-// The last 68 groups of a tile (448..515): the 224 producer threads keep two groups each in registers, these
-// are taken by 68 threads, out of line (the caller's 40 raw words stay in registers around the call).
-// phase 0 = residues 0-2, phase 1 = residues 3-4.  Block indices are absolute 8-sample blocks, clamped
-// like the inline loads.
-__device__ __noinline__ void tc_produce_extra(const uint4* __restrict__ pcm16, int32_t blk0, int32_t blo, int32_t bhi,
-                                              uint8_t* sA, int g, int phase) {
-  uint4 raw[5];
-#pragma unroll
-  for (int q = 0; q < 5; ++q) raw[q] = __ldg(pcm16 + min(max(blk0 + 5 * g + q, blo), bhi));
-  uint32_t w[20];
-  tc_xor_words(raw, w);
-  const uint32_t ph = tc_stream_offset(g);
-  if (phase == 0) {
-    tc_produce_res<0>(w, sA, ph);
-    tc_produce_res<1>(w, sA, ph);
-    tc_produce_res<2>(w, sA, ph);
-  } else {
-    tc_produce_res<3>(w, sA, ph);
-    tc_produce_res<4>(w, sA, ph);
-  }
-}
-
 // One group, all residues (slow path only).  Out of line.
 __device__ __noinline__ void tc_produce_group(uint4 r0, uint4 r1, uint4 r2, uint4 r3, uint4 r4, uint8_t* sA, int g) {
   const uint4 raw[5] = {r0, r1, r2, r3, r4};

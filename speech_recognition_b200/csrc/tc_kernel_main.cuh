@@ -303,6 +303,13 @@ __device__ __noinline__ void tc_draw_tables(int32_t* tab, const TcDrawArgs p, co
   tc::named_bar_sync(13, kTcEpilogueThreads);
 }
 
+// warpgroup-wide register re-allocation relative to the launch allocation (nothing to do when equal)
+template <int N>
+__device__ __forceinline__ void tc_set_regs() {
+  if (N < kTcLaunchRegs) tc::setmaxnreg_dec<N>();
+  if (N > kTcLaunchRegs) tc::setmaxnreg_inc<N>();
+}
+
 template <int C, bool kMask>
 __global__ void __launch_bounds__(kTcThreads, 1)
     tc_frontend_kernel(const KernelParams p, const TcParams tp, const __grid_constant__ CUtensorMap out_map) {
@@ -382,7 +389,7 @@ __global__ void __launch_bounds__(kTcThreads, 1)
 
   if (warp >= 1 && warp < 8) {
     // ======================= PRODUCERS (warps 1-7: 224 threads) =================================
-    if (kTcRegsProducer < kTcLaunchRegs) tc::setmaxnreg_dec<kTcRegsProducer>();
+    tc_set_regs<kTcRegsProducer>();
     // One A stage, refilled in two phases: the streams of residues 0-2 as soon as the previous tile's
     // MMAs of those residues have completed, residues 3-4 after the rest (those MMAs wait for the
     // epilogue to release TMEM).  The raw PCM of the NEXT tile is loaded into the same registers at
@@ -390,15 +397,15 @@ __global__ void __launch_bounds__(kTcThreads, 1)
     const int ptid = tid - 32;
     uint32_t n = 0;  // active tiles processed so far by this CTA
     // 516 groups of 40 samples = 129 hops (128 frames + the half-row of overlap): groups ptid and
-    // ptid + 224 for every thread, held in registers (and preloaded for the next tile); the last 68 groups
-    // go to threads 0..67, out of line and loaded on the spot (their range is in L2): the producers' register
-    // budget holds two groups of raw words, not three
-    const bool extra = ptid < 516 - 2 * kTcProducerThreads;
-    uint32_t ph[2];
+    // ptid + 224 for every thread, ptid + 448 for the first 68 - all held in registers and preloaded for
+    // the next tile.  (Loading the third group on the spot, out of line, to save 20 registers was measured:
+    // the L2 round trips of those three warps sit on the a_full barrier - 83.1 vs 79.5 us per launch.)
+    const bool third = ptid < 516 - 2 * kTcProducerThreads;
+    uint32_t ph[3];
 #pragma unroll
-    for (int i = 0; i < 2; ++i) ph[i] = tc_stream_offset(ptid + kTcProducerThreads * i);
+    for (int i = 0; i < 3; ++i) ph[i] = tc_stream_offset(ptid + kTcProducerThreads * i);
     const uint4* pcm16 = reinterpret_cast<const uint4*>(p.pcm);
-    uint32_t w[2][20];  // this thread's groups: raw words (two samples each), XOR-ed in place before use
+    uint32_t w[3][20];  // this thread's groups: raw words (two samples each), XOR-ed in place before use
     bool preloaded = false;
     // raw words of one tile -> w: absolute 8-sample block index, clamped into the utterance
 #define TC_LOAD_GROUP(I, BLK0, BLO, BHI)                                                               \
@@ -412,7 +419,7 @@ __global__ void __launch_bounds__(kTcThreads, 1)
   }
     if (!tc::mbar_wait(&ctl->list_full, 0)) timed_out = true;
     const int n_tiles = ctl->n_tiles;
-    // Register budget: the 40 raw words of the NEXT tile are live across the top of the loop, so
+    // Register budget: the 60 raw words of the NEXT tile are live across the top of the loop, so
     // nothing about the tiles is carried in registers - every use re-reads the list entry.
     // next tile: first block and clamp range, all in absolute 8-sample blocks (< 2^31 blocks)
 #define TC_NEXT_RANGE()                                                                           \
@@ -441,9 +448,10 @@ __global__ void __launch_bounds__(kTcThreads, 1)
           const int32_t b_0 = b_lo + 20 * (cur.y * tp.tout - tp.halo);
           TC_LOAD_GROUP(0, b_0, b_lo, b_hi)
           TC_LOAD_GROUP(1, b_0, b_lo, b_hi)
+          if (third) { TC_LOAD_GROUP(2, b_0, b_lo, b_hi) }
         }
 #pragma unroll
-        for (int i = 0; i < 2; ++i)
+        for (int i = 0; i < 3; ++i)
 #pragma unroll
           for (int k = 0; k < 20; ++k) w[i][k] ^= 0x80008000u;
         if (ptid == 0) { TC_STAMP(0, n, 1) }
@@ -456,11 +464,10 @@ __global__ void __launch_bounds__(kTcThreads, 1)
         tc_produce_res<0>(w[1], sA, ph[1]);
         tc_produce_res<1>(w[1], sA, ph[1]);
         tc_produce_res<2>(w[1], sA, ph[1]);
-        if (extra) {
-          const int4 cur = sList[ti];
-          const int32_t b_lo = cur.w;
-          tc_produce_extra(pcm16, b_lo + 20 * (cur.y * tp.tout - tp.halo), b_lo, b_lo + (cur.z >> 3) - 1, sA,
-                           ptid + 2 * kTcProducerThreads, 0);
+        if (third) {
+          tc_produce_res<0>(w[2], sA, ph[2]);
+          tc_produce_res<1>(w[2], sA, ph[2]);
+          tc_produce_res<2>(w[2], sA, ph[2]);
         }
         tc::fence_async_smem();  // generic-proxy writes -> visible to the tensor core (async proxy)
         tc::mbar_arrive(&ctl->a_full[0]);
@@ -472,11 +479,9 @@ __global__ void __launch_bounds__(kTcThreads, 1)
         tc_produce_res<4>(w[0], sA, ph[0]);
         tc_produce_res<3>(w[1], sA, ph[1]);
         tc_produce_res<4>(w[1], sA, ph[1]);
-        if (extra) {
-          const int4 cur = sList[ti];
-          const int32_t b_lo = cur.w;
-          tc_produce_extra(pcm16, b_lo + 20 * (cur.y * tp.tout - tp.halo), b_lo, b_lo + (cur.z >> 3) - 1, sA,
-                           ptid + 2 * kTcProducerThreads, 1);
+        if (third) {
+          tc_produce_res<3>(w[2], sA, ph[2]);
+          tc_produce_res<4>(w[2], sA, ph[2]);
         }
         tc::fence_async_smem();
         tc::mbar_arrive(&ctl->a_full[1]);
@@ -487,6 +492,7 @@ __global__ void __launch_bounds__(kTcThreads, 1)
           TC_NEXT_RANGE()
           TC_LOAD_GROUP(0, nb_0, nb_lo, nb_hi)
           TC_LOAD_GROUP(1, nb_0, nb_lo, nb_hi)
+          if (third) { TC_LOAD_GROUP(2, nb_0, nb_lo, nb_hi) }
         }
         preloaded = next_ok;
         if (ptid == 0) { TC_STAMP(0, n, 6) }
@@ -509,7 +515,7 @@ __global__ void __launch_bounds__(kTcThreads, 1)
     // Warp 0 on purpose: the issuing thread needs an instruction slot every few cycles to keep the
     // tensor pipe fed, and the warp schedulers favour the oldest (lowest) warp of a sub-partition -
     // as the youngest warp it was starved by the epilogue warps (96 instead of 60 cycles per MMA).
-    if (kTcRegsProducer < kTcLaunchRegs) tc::setmaxnreg_dec<kTcRegsProducer>();
+    tc_set_regs<kTcRegsProducer>();
     if (tc::elect_one()) {
       // the issuer only needs the NUMBER of tiles of this CTA (every tile of the list is active)
       if (!tc::mbar_wait(&ctl->list_full, 0)) timed_out = true;
@@ -571,7 +577,7 @@ __global__ void __launch_bounds__(kTcThreads, 1)
     // its own mel accumulators (only the bins its FFT bins feed).  Values travel down the chain A -> B -> C
     // through the hand-over zone: partial sums of bins two groups feed, and finished values on their way to
     // the group that stores their float4 group.  C then stores the 32 rows with one TMA tensor store.
-    if (kTcRegsEpilogue > kTcLaunchRegs) tc::setmaxnreg_inc<kTcRegsEpilogue>();
+    tc_set_regs<kTcRegsEpilogue>();
     // C == 1: masks are applied to the finished values in registers (measured 102.7 -> 96.7 us on config 3);
     // C == 3: on the staged row before the copy-out
     constexpr bool kRegMask = kMask && C == 1;
@@ -715,10 +721,10 @@ __global__ void __launch_bounds__(kTcThreads, 1)
         }
         if (tm) mb0 = mb1 = mb2 = 0xffffffffu;
       }
-      if (lane == 0 && wq == 0) { TC_STAMP(2, n, 0) }
+      if (lane == 0 && wq == 0) { TC_STAMP(2 + group, n, 0) }
       if (!timed_out && !tc::mbar_wait(&ctl->acc_full, n & 1)) timed_out = true;
       tc::tc_fence_after();
-      if (lane == 0 && wq == 0) { TC_STAMP(2, n, 1) }
+      if (lane == 0 && wq == 0) { TC_STAMP(2 + group, n, 1) }
       const uint32_t t_tile = tmem_base + lane_base;
       // One group's pass over its quads: five TMEM loads (one per residue) of four columns, the packed
       // radix-5 + power step, the quad's mel FFMAs (immediates, named accumulators).  The TMEM slots go
@@ -726,10 +732,16 @@ __global__ void __launch_bounds__(kTcThreads, 1)
       // C == 1: the staged rows and the hand-over zone of the previous tile are free once group C's TMA
       // store has read them and C's phase 2 is over - C says so at its first quad (`CFREE`), A and B check
       // before their first write (`ABFREE`), long after.
+#ifndef TC_LOOP_MODE
+#define TC_LOOP_MODE 0   // measured: rolled 78.7 us, straight-line + software-pipelined 87.9 us per launch (see below)
+#endif
+#define TC_QUAD_ADDR(Q, R) (t_tile + (((5u * n + (R)) & 7u) << 6) + 4 * (Q))
+#if TC_LOOP_MODE == 0
+      // rolled loop, one quad per iteration: load, wait, compute
 #define TC_GROUP_LOOP(G, Q0, Q1, CFREE)                                                           \
   float P[11], d[5][4];                                                                           \
   _Pragma("unroll 1") for (int q = (Q0); q < (Q1); ++q) {                                         \
-    _Pragma("unroll") for (int r = 0; r < 5; ++r) tc::tmem_ld4(t_tile + (((5u * n + r) & 7u) << 6) + 4 * q, d[r]); \
+    _Pragma("unroll") for (int r = 0; r < 5; ++r) tc::tmem_ld4(TC_QUAD_ADDR(q, r), d[r]);         \
     tc::tmem_ld_wait();                                                                           \
     if (q == (Q1) - 1) {                                                                          \
       tc::tc_fence_before();                                                                      \
@@ -741,18 +753,46 @@ __global__ void __launch_bounds__(kTcThreads, 1)
     if (q == (Q0)) { CFREE }                                                                      \
     TC_G##G##_SWITCH(q, P);                                                                       \
   }
+#else
+      // straight-line code, software-pipelined: the next quad's five TMEM loads are in flight while the
+      // current quad's butterflies and mel FFMAs run.  Measured (r2d): the groups' read phase shrinks from
+      // 3.3-3.9 k to 2.8-3.2 k cycles, but the producers, on the same sub-partitions, take 2.9 k instead of
+      // 1.5 k cycles for their first phase and the launch gets slower (87.9 vs 78.7 us): the sub-partitions'
+      // issue slots / FMA pipe are what the roles compete for, not latency.  Kept for experiments.
+#define TC_GROUP_LOOP(G, Q0, Q1, CFREE)                                                           \
+  float P[11], d[2][5][4];                                                                        \
+  _Pragma("unroll") for (int r = 0; r < 5; ++r) tc::tmem_ld4(TC_QUAD_ADDR((Q0), r), d[0][r]);     \
+  _Pragma("unroll") for (int q = (Q0); q < (Q1); ++q) {                                           \
+    tc::tmem_ld_wait();                                                                           \
+    if (q + 1 < (Q1)) {                                                                           \
+      _Pragma("unroll") for (int r = 0; r < 5; ++r) tc::tmem_ld4(TC_QUAD_ADDR(q + 1, r), d[(q + 1 - (Q0)) & 1][r]); \
+    } else {                                                                                      \
+      tc::tc_fence_before();                                                                      \
+      tc::mbar_arrive(&ctl->acc_empty);                                                           \
+      if (lane == 0 && wq == 0) { TC_STAMP(2 + (G), n, 2) }                                       \
+    }                                                                                             \
+    if ((G) == 0 && q == 0) tc_radix5_power_special(d[(q - (Q0)) & 1], P);                        \
+    else tc_radix5_power_pair(d[(q - (Q0)) & 1], P);                                              \
+    if (q == (Q0)) { CFREE }                                                                      \
+    TC_G##G##_SWITCH(q, P);                                                                       \
+  }
+#endif
       if (group == 0) {
         TC_G0_DECL
         TC_GROUP_LOOP(0, 0, TC_SPLIT_A, )
+        if (lane == 0 && wq == 0) { TC_STAMP(2, n, 3) }
         if (C == 1) tc::named_bar_sync(bar_free, 96);
         TC_G0_PHASE1;
         tc::named_bar_arrive(bar_ab, 64);
       } else if (group == 1) {
         TC_G1_DECL
         TC_GROUP_LOOP(1, TC_SPLIT_A, TC_SPLIT_B, )
+        if (lane == 0 && wq == 0) { TC_STAMP(3, n, 3) }
         if (C == 1) tc::named_bar_sync(bar_free, 96);
         TC_G1_PHASE1;
+        if (lane == 0 && wq == 0) { TC_STAMP(3, n, 4) }
         tc::named_bar_sync(bar_ab, 64);
+        if (lane == 0 && wq == 0) { TC_STAMP(3, n, 6) }
         { TC_G1_PHASE2; }
         tc::named_bar_arrive(bar_bc, 64);
       } else {
@@ -763,13 +803,17 @@ __global__ void __launch_bounds__(kTcThreads, 1)
                         __syncwarp();
                         tc::named_bar_arrive(bar_free, 96);
                       })
+        if (lane == 0 && wq == 0) { TC_STAMP(4, n, 3) }
         TC_G2_PHASE1;
+        if (lane == 0 && wq == 0) { TC_STAMP(4, n, 4) }
         tc::named_bar_sync(bar_bc, 64);
+        if (lane == 0 && wq == 0) { TC_STAMP(4, n, 6) }
         { TC_G2_PHASE2; }
         if (kMask && !kRegMask) tc_mask_row(out_row, mask_entry, p.n_masks_f, p.n_masks_t, t_row, t_row >= 0 && t_row < n_fr);
       }
 #undef TC_GROUP_LOOP
-      if (lane == 0 && wq == 0) { TC_STAMP(2, n, 3) }
+#undef TC_QUAD_ADDR
+      if (lane == 0 && wq == 0) { TC_STAMP(2 + group, n, 5) }
       ++n;
 
       if (C == 1) {
@@ -790,6 +834,7 @@ __global__ void __launch_bounds__(kTcThreads, 1)
               issuer = true;
             }
           }
+          if (lane == 0 && wq == 0) { TC_STAMP(4, n - 1, 7) }
         }
       } else {
         tc::named_bar_sync(14, kTcEpilogueThreads);  // staged (and masked) rows visible to the 12 epilogue warps
