@@ -20,9 +20,9 @@
 //   * the radix-5 stage over r, power, sparse mel (FFMA immediates), log and the SpecAugment /
 //     delta / padding epilogue run on the CUDA cores, one thread per frame, straight from TMEM.
 //
-// Roles (640 threads, one persistent CTA per SM, tiles of 128 frames): warp 0 MMA issuer, warps 1-7
-// producers (PCM -> exact f16 hi/lo streams), warps 8-19 three epilogue groups (thread = frame = TMEM
-// lane, each group reduces a third of the accumulator columns).  TMEM is used as a ring of eight
+// Roles (one persistent CTA per SM, tiles of 128 frames): warp 0 MMA issuer, warps 1-7 producers (PCM ->
+// exact f16 hi/lo streams), warps 8.. two or three epilogue groups (thread = frame = TMEM lane, each
+// group reduces its share of the accumulator columns).  TMEM is used as a ring of eight
 // 64-column accumulator slots (a tile needs five); shared memory holds B (80 KB), one A stage (85 KB),
 // the output staging tile (42 KB) and the epilogue groups' hand-over zone (10 KB).  DESIGN.md section
 // 4.1 has the pipeline and the measurements.
@@ -62,26 +62,41 @@ constexpr int kTcSmemList = kTcSmemWalk + 512;                 // the CTA's tile
 constexpr int kTcListTiles = 256;                              // ... at most this many per CTA and launch
 constexpr int kTcSmemTotal = kTcSmemList + kTcListTiles * 16 + 1024;  // + alignment slack
 static_assert(kTcSmemTotal <= 232448, "shared memory budget (227 KB per CTA)");
-// Warps: 0 = MMA issuer, 1-7 = producers (224 threads), 8-19 = epilogue groups A, B, C (3 x 4 warps,
-// warp % 4 = TMEM lane quadrant).  20 warps on purpose: registers are allocated to a CTA in units of four
-// warps, so 21 warps would be charged as 24 (80 registers per thread at launch instead of 96).  The launch
-// allocates 96 registers per thread (640 x 96 = 60 K of the 64 K) and every role fits: each epilogue group
-// keeps only the ~34 mel accumulators its own FFT bins feed (ptxas: no spills), the producers hold up to
-// three groups of raw words.  TC_REGS_E / TC_REGS_P (variant builds) move registers between the roles with
-// setmaxnreg, within 8 x 32 x P + 12 x 32 x E <= 61 440.
+// Warps: 0 = MMA issuer, 1-7 = producers (224 threads), then TC_NGROUPS epilogue groups of 4 warps
+// (warp % 4 = TMEM lane quadrant): A, (B,) C.  TC_NGROUPS comes with the generated tables (two groups when
+// the middle group's quad range is empty).
+//   3 groups: 20 warps.  (Not 21: registers are allocated to a CTA in units of four warps.)  The launch
+//             allocates 96 registers per thread (640 x 96 = 60 K of the 64 K); setmaxnreg moves registers
+//             between the roles within 8 x 32 x P + 12 x 32 x E <= 61 440.
+//   2 groups: 16 warps, 128 registers per thread at launch; 8 x 32 x 96 + 8 x 32 x 160 = 65 536.  The
+//             epilogue threads are fewer and fatter: the registers hold the last TC_TAIL_K quads of a
+//             tile, so that the TMEM slots go back to the MMA issuer before the arithmetic on them.
+#if TC_NGROUPS == 3
 #ifndef TC_REGS_E
 #define TC_REGS_E 88
 #endif
 #ifndef TC_REGS_P
 #define TC_REGS_P 104
 #endif
-constexpr int kTcThreads = 640;
 constexpr int kTcLaunchRegs = 96;
+#else
+#ifndef TC_REGS_E
+#define TC_REGS_E 160
+#endif
+#ifndef TC_REGS_P
+#define TC_REGS_P 96
+#endif
+constexpr int kTcLaunchRegs = 128;
+#endif
+#ifndef TC_TAIL_K
+#define TC_TAIL_K 1    // quads of a tile held in registers when the TMEM slots are released
+#endif
+constexpr int kTcEpilogueThreads = 128 * TC_NGROUPS;
+constexpr int kTcThreads = 256 + kTcEpilogueThreads;
 constexpr int kTcMmaWarp = 0;
 constexpr int kTcProducerThreads = 224;
-constexpr int kTcEpilogueThreads = 384;
 constexpr int kTcRegsEpilogue = TC_REGS_E, kTcRegsProducer = TC_REGS_P;
-static_assert(8 * 32 * kTcRegsProducer + 12 * 32 * kTcRegsEpilogue <= kTcThreads * kTcLaunchRegs, "register pool");
+static_assert(8 * 32 * kTcRegsProducer + 4 * TC_NGROUPS * 32 * kTcRegsEpilogue <= kTcThreads * kTcLaunchRegs, "register pool");
 constexpr int kTcBScaleLog2 = 10;          // B is stored as 2^10 * w * twiddle
 // power = |Y|^2 * 2^(-2*10) (B scale) * 2^(-30) (int16 -> [-1, 1) twice)
 #define TC_PSCALE 0x1p-50f

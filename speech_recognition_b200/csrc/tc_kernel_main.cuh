@@ -15,18 +15,19 @@ struct TcCtl {
   int32_t n_tiles;      // length of the tile list
 };
 
-// log(mel + eps): one MUFU.LG2 + one FMUL (abs error ~ 2^-22 * |log|; mel + eps >= eps is a normal
-// float).  Silence must give exactly logf(eps) - the reference's golden fixture pins that value - and
-// it does: acc = 0 makes the argument eps itself, and tc_eps_probe_kernel checks at handle creation
-// that this expression reproduces logf(eps) bit-for-bit (true for the reference's 1e-12); a handle
-// whose epsilon fails the probe does not get the tensor-core kernel.
+// log(mel + eps): one MUFU.LG2 + one FMUL (abs error ~ 2^-22 * |log|).  The epsilon is not added here: it
+// is the initial value of the bin's accumulator (tc_tables_generated.inc), so `v` is mel + eps already,
+// a normal float >= eps.  Silence must give exactly logf(eps) - the reference's golden fixture pins that
+// value - and it does: the accumulator is then eps itself, and tc_eps_probe_kernel checks at handle
+// creation that this expression reproduces logf(eps) bit-for-bit (true for the reference's 1e-12); a
+// handle whose epsilon fails the probe does not get the tensor-core kernel.
 __device__ __forceinline__ float tc_log_fast(float v) {
   float l2;
   asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(l2) : "f"(v));
   return l2 * 0.69314718055994530942f;
 }
-__device__ __forceinline__ float tc_finish(float acc, float eps, float) { return tc_log_fast(acc + eps); }
-__global__ void tc_eps_probe_kernel(float eps, float* out) { out[0] = tc_log_fast(0.0f + eps); }
+__device__ __forceinline__ float tc_finish(float acc, float, float) { return tc_log_fast(acc); }
+__global__ void tc_eps_probe_kernel(float eps, float* out) { out[0] = tc_log_fast(eps); }
 
 #if defined(TC_ABLATE_ESTS)
 #define TC_ROW_ST(PTR, V) if (eps == 12345.0f) *(PTR) = (V) /* (experiment: no staging stores) */
@@ -581,7 +582,8 @@ __global__ void __launch_bounds__(kTcThreads, 1)
     // C == 1: masks are applied to the finished values in registers (measured 102.7 -> 96.7 us on config 3);
     // C == 3: on the staged row before the copy-out
     constexpr bool kRegMask = kMask && C == 1;
-    const int group = (warp - 8) >> 2, wq = warp & 3;
+    // (two groups: the second one is "group 2" - the last group - in the generated code as well)
+    const int group = TC_NGROUPS == 3 ? (warp - 8) >> 2 : ((warp - 8) >> 2) * 2, wq = warp & 3;
     const int etid = tid - 256;
     const int row = wq * 32 + lane;
     uint32_t n = 0;
@@ -591,8 +593,10 @@ __global__ void __launch_bounds__(kTcThreads, 1)
     float* park_row = sPark + row * TC_PARK_PITCH;
     const uint32_t sOut_s = tc::smem_u32(sOut);
     const uint32_t lane_base = static_cast<uint32_t>(wq * 32) << 16;
-    // trio barriers: "rows free" C -> A, B (96 threads); A -> B and B -> C hand-overs (64 threads)
+    // barriers of the warps that share 32 rows: "rows free" C -> A (, B); hand-overs A -> B, B -> C (64 threads;
+    // two groups: A -> C on bar_bc)
     const uint32_t bar_free = 1 + wq, bar_ab = 5 + wq, bar_bc = 9 + wq;
+    constexpr uint32_t kFreeCount = 32 * TC_NGROUPS;
     bool issuer = false;  // (group C) this thread issued the trio's TMA stores (bulk async-groups are per thread)
     int32_t* sMask = reinterpret_cast<int32_t*>(smem + kTcSmemMask);
     // the first epilogue warp of the grid also reports the frame counts, and flags the zero-frame
@@ -737,21 +741,33 @@ __global__ void __launch_bounds__(kTcThreads, 1)
 #endif
 #define TC_QUAD_ADDR(Q, R) (t_tile + (((5u * n + (R)) & 7u) << 6) + 4 * (Q))
 #if TC_LOOP_MODE == 0
-      // rolled loop, one quad per iteration: load, wait, compute
+      // rolled loop, one quad per iteration: load, wait, compute - except the last TC_TAIL_K quads, which are
+      // loaded together into registers BEFORE the arithmetic on them: the chain "TMEM read phase -> release
+      // -> the next tile's MMAs of residues 3-4 -> acc_full" is what the tile period is made of, and every
+      // quad of arithmetic taken out of the read phase shortens it.
+#define TC_QUAD_MATH(G, QQ, D)                                                                    \
+    if ((G) == 0 && (QQ) == 0) tc_radix5_power_special(D, P);                                     \
+    else tc_radix5_power_pair(D, P);
 #define TC_GROUP_LOOP(G, Q0, Q1, CFREE)                                                           \
-  float P[11], d[5][4];                                                                           \
-  _Pragma("unroll 1") for (int q = (Q0); q < (Q1); ++q) {                                         \
-    _Pragma("unroll") for (int r = 0; r < 5; ++r) tc::tmem_ld4(TC_QUAD_ADDR(q, r), d[r]);         \
+  float P[11], d[TC_TAIL_K][5][4];                                                                \
+  constexpr int kTail = (Q1) - (Q0) < TC_TAIL_K ? (Q1) - (Q0) : TC_TAIL_K;                        \
+  _Pragma("unroll 1") for (int q = (Q0); q < (Q1) - kTail; ++q) {                                 \
+    _Pragma("unroll") for (int r = 0; r < 5; ++r) tc::tmem_ld4(TC_QUAD_ADDR(q, r), d[0][r]);      \
     tc::tmem_ld_wait();                                                                           \
-    if (q == (Q1) - 1) {                                                                          \
-      tc::tc_fence_before();                                                                      \
-      tc::mbar_arrive(&ctl->acc_empty);                                                           \
-      if (lane == 0 && wq == 0) { TC_STAMP(2 + (G), n, 2) }                                       \
-    }                                                                                             \
-    if ((G) == 0 && q == 0) tc_radix5_power_special(d, P);                                        \
-    else tc_radix5_power_pair(d, P);                                                              \
+    TC_QUAD_MATH(G, q, d[0])                                                                      \
     if (q == (Q0)) { CFREE }                                                                      \
     TC_G##G##_SWITCH(q, P);                                                                       \
+  }                                                                                               \
+  _Pragma("unroll") for (int k = 0; k < kTail; ++k)                                               \
+    _Pragma("unroll") for (int r = 0; r < 5; ++r) tc::tmem_ld4(TC_QUAD_ADDR((Q1) - kTail + k, r), d[k][r]); \
+  tc::tmem_ld_wait();                                                                             \
+  tc::tc_fence_before();                                                                          \
+  tc::mbar_arrive(&ctl->acc_empty);                                                               \
+  if (lane == 0 && wq == 0) { TC_STAMP(2 + (G), n, 2) }                                           \
+  _Pragma("unroll") for (int k = 0; k < kTail; ++k) {                                             \
+    TC_QUAD_MATH(G, (Q1) - kTail + k, d[k])                                                       \
+    if ((Q1) - kTail + k == (Q0)) { CFREE }                                                       \
+    TC_G##G##_SWITCH((Q1) - kTail + k, P);                                                        \
   }
 #else
       // straight-line code, software-pipelined: the next quad's five TMEM loads are in flight while the
@@ -781,27 +797,29 @@ __global__ void __launch_bounds__(kTcThreads, 1)
         TC_G0_DECL
         TC_GROUP_LOOP(0, 0, TC_SPLIT_A, )
         if (lane == 0 && wq == 0) { TC_STAMP(2, n, 3) }
-        if (C == 1) tc::named_bar_sync(bar_free, 96);
+        if (C == 1) tc::named_bar_sync(bar_free, kFreeCount);
         TC_G0_PHASE1;
-        tc::named_bar_arrive(bar_ab, 64);
+        tc::named_bar_arrive(TC_NGROUPS == 3 ? bar_ab : bar_bc, 64);
+#if TC_NGROUPS == 3
       } else if (group == 1) {
         TC_G1_DECL
         TC_GROUP_LOOP(1, TC_SPLIT_A, TC_SPLIT_B, )
         if (lane == 0 && wq == 0) { TC_STAMP(3, n, 3) }
-        if (C == 1) tc::named_bar_sync(bar_free, 96);
+        if (C == 1) tc::named_bar_sync(bar_free, kFreeCount);
         TC_G1_PHASE1;
         if (lane == 0 && wq == 0) { TC_STAMP(3, n, 4) }
         tc::named_bar_sync(bar_ab, 64);
         if (lane == 0 && wq == 0) { TC_STAMP(3, n, 6) }
         { TC_G1_PHASE2; }
         tc::named_bar_arrive(bar_bc, 64);
+#endif
       } else {
         TC_G2_DECL
         TC_GROUP_LOOP(2, TC_SPLIT_B, 16,
                       if (C == 1) {
                         if (issuer) tc::bulk_wait_read(); /* async-groups belong to the thread that committed them */
                         __syncwarp();
-                        tc::named_bar_arrive(bar_free, 96);
+                        tc::named_bar_arrive(bar_free, kFreeCount);
                       })
         if (lane == 0 && wq == 0) { TC_STAMP(4, n, 3) }
         TC_G2_PHASE1;
@@ -813,6 +831,7 @@ __global__ void __launch_bounds__(kTcThreads, 1)
       }
 #undef TC_GROUP_LOOP
 #undef TC_QUAD_ADDR
+#undef TC_QUAD_MATH
       if (lane == 0 && wq == 0) { TC_STAMP(2 + group, n, 5) }
       ++n;
 
@@ -889,6 +908,7 @@ __global__ void __launch_bounds__(kTcThreads, 1)
     tc::st_global_v8(c_dst[S] + 8, o + 8);                                                             \
     tc::st_global_v8(c_dst[S] + 16, o + 16);                                                           \
   }
+        // 1280 items over 384 threads (4 rounds, the last one partial) or 256 threads (5 rounds)
         TC_CO_LOAD(0, 0)
         TC_CO_LOAD(1, 1)
         TC_CO_STORE(0)
@@ -896,7 +916,13 @@ __global__ void __launch_bounds__(kTcThreads, 1)
         TC_CO_STORE(1)
         TC_CO_LOAD(1, 3)
         TC_CO_STORE(0)
+#if TC_NGROUPS == 2
+        TC_CO_LOAD(0, 4)
         TC_CO_STORE(1)
+        TC_CO_STORE(0)
+#else
+        TC_CO_STORE(1)
+#endif
 #undef TC_CO_LOAD
 #undef TC_CO_STORE
         tc::named_bar_sync(14, kTcEpilogueThreads);  // the staging tile and the hand-over zone may be overwritten

@@ -30,7 +30,7 @@ static inline float tc_masked(float v, uint32_t b0, uint32_t b1, uint32_t b2) {
   const uint32_t w = M < 32 ? b0 : (M < 64 ? b1 : b2);
   return (w & (1u << (M & 31))) ? v * 0.0f : v;
 }
-#define TC_FIN(M_, A) tc_masked<(M_)>(logf((A) + eps), mb0, mb1, mb2)
+#define TC_FIN(M_, A) tc_masked<(M_)>(logf(A), mb0, mb1, mb2)   // (eps is the accumulators' initial value)
 #define TC_ST4(G, A, B, C_, D) do { out_row[4 * (G)] = (A); out_row[4 * (G) + 1] = (B); out_row[4 * (G) + 2] = (C_); out_row[4 * (G) + 3] = (D); } while (0)
 #define TC_PARK4(S, A, B, C_, D) do { park_row[4 * (S)] = (A); park_row[4 * (S) + 1] = (B); park_row[4 * (S) + 2] = (C_); park_row[4 * (S) + 3] = (D); } while (0)
 #define TC_UNPARK4(S) float4{park_row[4 * (S)], park_row[4 * (S) + 1], park_row[4 * (S) + 2], park_row[4 * (S) + 3]}
