@@ -2,6 +2,8 @@
 // (run/train.py:88-116) instead of the fused forward: SpecAugment draw / apply, delta.
 #pragma once
 
+#include <cstring>
+
 #include "common.cuh"
 
 namespace b200mel {
@@ -245,14 +247,209 @@ __global__ void __launch_bounds__(kMfccThreads)
 }
 
 // ---------------------------------------------------------------------------------------------
+// The same second stage with the DCT on the tensor cores (mma.sync m16n8k8, TF32 operands, float32
+// accumulators) for the shipped shape M = 80 and n_mfcc a multiple of 8 (kspon / clovacall: 40).
+// Float32 accuracy comes from the usual three-product split: x = xh + xl, d = dh + dl with every part
+// a TF32 number, x d ~ xl dh + xh dl + xh dh (the dropped xl dl term is 2^-22 relative).  The DCT
+// image (dh, dl) is split once on the host (b200mel_create) and copied as it is; the log-mel operand is
+// split in registers.  One block = 128 threads, tiles of 64 rows (warp w owns rows 16 w .. 16 w + 15),
+// `tiles_per_block` consecutive tiles of one utterance per block so that the DCT image and the mask
+// table are fetched once.  With deltas a tile recomputes the 2 rows before it (62 new rows per tile).
+// Copy-out items are (row, 8 coefficients): 32 bytes (C = 1) or 96 bytes (C = 3) of whole sectors,
+// written with 256-bit stores: `out` must be 32-byte aligned.
+// Pitches: log-mel rows 84 floats (A fragments: bank 20 g + t, conflict-free), DCT rows and coefficient
+// rows P = mfcc_mma_pitch(n_mfcc) with P mod 32 in {8, 24} (B fragments: bank 8 t + g).
+// ---------------------------------------------------------------------------------------------
+constexpr int kMfccMmaRows = 64, kMfccMmaThreads = 128, kMfccMmaM = 80, kMfccMmaPitchX = 84;
+__host__ __device__ constexpr int mfcc_mma_pitch(int n_mfcc) {
+  int p = n_mfcc;
+  while ((p & 31) != 8 && (p & 31) != 24) ++p;
+  return p;
+}
+inline size_t mfcc_post_mma_smem_bytes(int n_mfcc) {
+  const int P = mfcc_mma_pitch(n_mfcc);
+  const int x_floats = kMfccMmaRows * (kMfccMmaPitchX > P ? kMfccMmaPitchX : P);
+  return sizeof(float) * (static_cast<size_t>(x_floats) + 2u * kMfccMmaM * P);
+}
+// round-to-nearest (ties away) TF32 of a float, as bits: the host-side twin of cvt.rna.tf32.f32
+inline uint32_t mfcc_tf32_host(float x) {
+  uint32_t u;
+  std::memcpy(&u, &x, 4);
+  u = (u + 0x1000u) & 0xffffe000u;
+  return u;
+}
+__device__ __forceinline__ uint32_t mfcc_tf32(float x) {
+  uint32_t r;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+  return r;
+}
+__device__ __forceinline__ void mfcc_mma_tf32(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+  asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+               : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+               : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ void mfcc_st_v8(float* p, const float* v) {
+  asm volatile("st.global.v8.f32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(p), "f"(v[0]), "f"(v[1]), "f"(v[2]),
+               "f"(v[3]), "f"(v[4]), "f"(v[5]), "f"(v[6]), "f"(v[7])
+               : "memory");
+}
+
+template <int NT, int C>
+__global__ void __launch_bounds__(kMfccMmaThreads)
+    mfcc_post_mma_kernel(const float* __restrict__ lm, float* __restrict__ out, const int32_t* __restrict__ lengths,
+                         int64_t t_max, int Lw, int H, const uint32_t* __restrict__ dct_image, int tiles_per_block,
+                         int n_masks_f, int n_masks_t, int sa_F, int sa_T, float sa_p,
+                         const int32_t* __restrict__ mask_table, uint64_t seed, uint64_t first_utt, int32_t* status,
+                         const int32_t* __restrict__ gate, int gate_value) {
+  extern __shared__ __align__(16) float mfcc_smem[];
+  if (gate && (*gate != 0) != (gate_value != 0)) return;
+  constexpr int M = kMfccMmaM, n_mfcc = 8 * NT, P = mfcc_mma_pitch(n_mfcc), PX = kMfccMmaPitchX;
+  constexpr int halo = C == 3 ? 2 : 0, new_rows = kMfccMmaRows - halo;
+  constexpr int x_floats = kMfccMmaRows * (PX > P ? PX : P);
+  float* sx = mfcc_smem;                                          // [64][PX] log-mel rows, then [64][P] coefficients
+  uint32_t* sd = reinterpret_cast<uint32_t*>(mfcc_smem + x_floats);  // [2][M][P] TF32 (hi, lo) of the DCT matrix
+  __shared__ int32_t s_table[2 * kMaxMasks];
+  const int b = blockIdx.y;
+  const int64_t n_tiles = (t_max + new_rows - 1) / new_rows;
+  const int64_t tile0 = static_cast<int64_t>(blockIdx.x) * tiles_per_block;
+  if (tile0 >= n_tiles) return;
+  const int64_t tile1 = tile0 + tiles_per_block < n_tiles ? tile0 + tiles_per_block : n_tiles;
+  const int32_t n_fr_all = frames_of(lengths[b], Lw, H);
+  const int64_t n_fr = n_fr_all < t_max ? n_fr_all : t_max;
+  const int n_masks = n_masks_f + n_masks_t;
+  if (threadIdx.x == 0 && n_masks > 0) {
+    if (mask_table) {
+      for (int i = 0; i < 2 * n_masks; ++i) s_table[i] = mask_table[static_cast<size_t>(b) * 2 * n_masks + i];
+    } else {
+      const int bad = specaug_draw_table(n_fr_all, n_mfcc, sa_F, n_masks_f, sa_T, sa_p, n_masks_t, seed,
+                                         first_utt + static_cast<uint64_t>(b), s_table);
+      if (bad && blockIdx.x == 0 && status) atomicOr(status, 1);
+    }
+  }
+  if (tile0 * new_rows - halo < n_fr)  // (a block that only writes padding never reads the matrix)
+    for (int i = threadIdx.x; i < 2 * M * P / 4; i += kMfccMmaThreads)
+      reinterpret_cast<uint4*>(sd)[i] = __ldg(reinterpret_cast<const uint4*>(dct_image) + i);
+  const float* lmb = lm + static_cast<int64_t>(b) * t_max * M;
+  float* outb = out + static_cast<int64_t>(b) * t_max * n_mfcc * C;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, tq = lane & 3;
+  for (int64_t tile = tile0; tile < tile1; ++tile) {
+    const int64_t t0 = tile * new_rows;                           // first row this tile writes
+    const int n_rows = t_max - t0 < new_rows ? static_cast<int>(t_max - t0) : new_rows;
+    if (t0 - halo >= n_fr) {
+      // padding only: +0.0 in every channel
+      const float z[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+      const int n8 = n_rows * n_mfcc * C / 8;
+      float* o = outb + t0 * n_mfcc * C;
+      for (int i = threadIdx.x; i < n8; i += kMfccMmaThreads) mfcc_st_v8(o + 8 * i, z);
+      continue;
+    }
+    // ---- log-mel rows t0 - halo .. t0 - halo + 63 (zero outside [0, n_fr)) ----
+    for (int i = threadIdx.x; i < kMfccMmaRows * (M / 4); i += kMfccMmaThreads) {
+      const int r = i / (M / 4), q = i - r * (M / 4);
+      const int64_t t = t0 - halo + r;
+      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (t >= 0 && t < n_fr) v = __ldg(reinterpret_cast<const float4*>(lmb + t * M) + q);
+      *reinterpret_cast<float4*>(sx + r * PX + 4 * q) = v;
+    }
+    __syncthreads();
+    float acc[NT][4];
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+      for (int i = 0; i < 4; ++i) acc[nt][i] = 0.0f;
+    const float* xa = sx + (16 * warp + g) * PX + tq;
+#pragma unroll 2
+    for (int ks = 0; ks < M / 8; ++ks) {
+      const float a[4] = {xa[8 * ks], xa[8 * ks + 8 * PX], xa[8 * ks + 4], xa[8 * ks + 8 * PX + 4]};
+      uint32_t ah[4], al[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        ah[i] = mfcc_tf32(a[i]);
+        al[i] = mfcc_tf32(a[i] - __uint_as_float(ah[i]));
+      }
+      const uint32_t* bh = sd + (8 * ks + tq) * P + g;
+      const uint32_t* bl = bh + M * P;
+#pragma unroll
+      for (int nt = 0; nt < NT; ++nt) {
+        const uint32_t h0 = bh[8 * nt], h1 = bh[8 * nt + 4 * P], l0 = bl[8 * nt], l1 = bl[8 * nt + 4 * P];
+        mfcc_mma_tf32(acc[nt], al, h0, h1);
+        mfcc_mma_tf32(acc[nt], ah, l0, l1);
+        mfcc_mma_tf32(acc[nt], ah, h0, h1);
+      }
+    }
+    __syncthreads();  // every read of the log-mel rows is done: the coefficients overwrite them
+#pragma unroll
+    for (int half = 0; half < 2; ++half) {
+      const int r = 16 * warp + g + 8 * half;
+      const int64_t t = t0 - halo + r;
+      const bool live = t >= 0 && t < n_fr;
+#pragma unroll
+      for (int nt = 0; nt < NT; ++nt) {
+        const int c = 8 * nt + 2 * tq;
+        float v0 = live ? acc[nt][2 * half] : 0.0f, v1 = live ? acc[nt][2 * half + 1] : 0.0f;
+        if (n_masks > 0 && live) {
+          v0 *= mask_value(s_table, n_masks_f, n_masks_t, static_cast<int>(t), c);
+          v1 *= mask_value(s_table, n_masks_f, n_masks_t, static_cast<int>(t), c + 1);
+        }
+        *reinterpret_cast<float2*>(sx + r * P + c) = make_float2(v0, v1);
+      }
+    }
+    __syncthreads();
+    // ---- copy-out: item = (row, 8 coefficients) ----
+    for (int i = threadIdx.x; i < n_rows * NT; i += kMfccMmaThreads) {
+      const int r = i / NT, j = i - r * NT;
+      const float* x0p = sx + (r + halo) * P + 8 * j;
+      float* o = outb + ((t0 + r) * n_mfcc + 8 * j) * C;
+      float x0[8];
+      *reinterpret_cast<float4*>(x0) = *reinterpret_cast<const float4*>(x0p);
+      *reinterpret_cast<float4*>(x0 + 4) = *reinterpret_cast<const float4*>(x0p + 4);
+      if (C == 1) {
+        mfcc_st_v8(o, x0);
+      } else {
+        float x1[8], x2[8], y[24];
+        *reinterpret_cast<float4*>(x1) = *reinterpret_cast<const float4*>(x0p - P);
+        *reinterpret_cast<float4*>(x1 + 4) = *reinterpret_cast<const float4*>(x0p - P + 4);
+        *reinterpret_cast<float4*>(x2) = *reinterpret_cast<const float4*>(x0p - 2 * P);
+        *reinterpret_cast<float4*>(x2 + 4) = *reinterpret_cast<const float4*>(x0p - 2 * P + 4);
+        const bool live = t0 + r < n_fr;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          const float d0 = x0[k] - x1[k], d1 = x1[k] - x2[k];
+          y[3 * k] = live ? x0[k] : 0.0f;
+          y[3 * k + 1] = live ? d0 : 0.0f;
+          y[3 * k + 2] = live ? d0 - d1 : 0.0f;
+        }
+        mfcc_st_v8(o, y);
+        mfcc_st_v8(o + 8, y + 8);
+        mfcc_st_v8(o + 16, y + 16);
+      }
+    }
+    __syncthreads();  // the next tile's rows overwrite the coefficients
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
 // float32 PCM entry of the tensor-core path.  The reference's audio is int16 / 32768 in float32
 // (load_audio_file, data.py:98-99, 104-105, 116): such samples convert back to int16 exactly and the
 // tensor-core kernel (whose operand split is exact for 16-bit samples) can take them.  Dense [B,
 // row_stride] input; only samples below lengths[b] are looked at.  *flag is set when a sample is not
 // an exact int16 / 32768: the tensor-core launch then does nothing and the generic kernel runs.
+// A streaming kernel: every thread keeps four groups of 8 samples (eight 128-bit loads) in flight and
+// the flag is polled once per round; the conversion itself is the magic-number round trip
+// (x * 32768 + 1.5 * 2^23: the low 16 bits of the sum ARE the two's-complement sample, and subtracting
+// the constant again returns x * 32768 exactly when x was an int16 / 32768).
 // ---------------------------------------------------------------------------------------------
-__global__ void pcm_f32_to_i16_kernel(const float* __restrict__ in, const int32_t* __restrict__ lengths, int64_t row_stride,
-                                      int16_t* __restrict__ out, int32_t* flag) {
+__device__ __forceinline__ uint32_t pcm_f32_pair(float x0, float x1, bool& bad) {
+  const float kMagic = 12582912.0f;
+  const float s0 = x0 * 32768.0f, s1 = x1 * 32768.0f;
+  const float m0 = s0 + kMagic, m1 = s1 + kMagic;
+  // (NaN fails both range tests; the range test first: outside [-1, 1) the sum's low bits mean nothing)
+  bad = bad || !(x0 >= -1.0f && x0 < 1.0f && x1 >= -1.0f && x1 < 1.0f && m0 - kMagic == s0 && m1 - kMagic == s1);
+  return (__float_as_uint(m0) & 0xffffu) | (__float_as_uint(m1) << 16);
+}
+__global__ void __launch_bounds__(256)
+    pcm_f32_to_i16_kernel(const float* __restrict__ in, const int32_t* __restrict__ lengths, int64_t row_stride,
+                          int16_t* __restrict__ out, int32_t* flag) {
   const int b = blockIdx.y;
   const int64_t len = lengths[b];
   const float* x = in + static_cast<int64_t>(b) * row_stride;
@@ -260,28 +457,38 @@ __global__ void pcm_f32_to_i16_kernel(const float* __restrict__ in, const int32_
   bool bad = false;
   const bool vec = (row_stride & 7) == 0 && (reinterpret_cast<uintptr_t>(in) & 31) == 0;
   const int64_t n8 = vec ? len >> 3 : 0;
-  for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n8;
-       i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+  const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
+  int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const float4* x4 = reinterpret_cast<const float4*>(x);
+  for (; i + 3 * stride < n8; i += 4 * stride) {
     if (*reinterpret_cast<volatile int32_t*>(flag) != 0) return;  // already decided: stop converting
-    const float4 a = __ldg(reinterpret_cast<const float4*>(x) + 2 * i), c = __ldg(reinterpret_cast<const float4*>(x) + 2 * i + 1);
-    const float v[8] = {a.x, a.y, a.z, a.w, c.x, c.y, c.z, c.w};
-    uint32_t w[4];
+    float4 v[8];
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
-      const float s0 = v[2 * k] * 32768.0f, s1 = v[2 * k + 1] * 32768.0f;
-      const float r0 = rintf(s0), r1 = rintf(s1);
-      bad = bad || !(r0 == s0 && r1 == s1 && fabsf(s0) <= 32768.0f && fabsf(s1) <= 32768.0f && s0 != 32768.0f && s1 != 32768.0f);
-      w[k] = (static_cast<uint32_t>(static_cast<int32_t>(r0)) & 0xffffu) | (static_cast<uint32_t>(static_cast<int32_t>(r1)) << 16);
+      v[2 * k] = __ldcs(x4 + 2 * (i + k * stride));
+      v[2 * k + 1] = __ldcs(x4 + 2 * (i + k * stride) + 1);
     }
-    *reinterpret_cast<uint4*>(y + 8 * i) = make_uint4(w[0], w[1], w[2], w[3]);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const float4 a = v[2 * k], c = v[2 * k + 1];
+      *reinterpret_cast<uint4*>(y + 8 * (i + k * stride)) =
+          make_uint4(pcm_f32_pair(a.x, a.y, bad), pcm_f32_pair(a.z, a.w, bad), pcm_f32_pair(c.x, c.y, bad),
+                     pcm_f32_pair(c.z, c.w, bad));
+    }
   }
-  for (int64_t i = 8 * n8 + static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < len;
-       i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
-    const float s0 = __ldg(x + i) * 32768.0f, r0 = rintf(s0);
-    bad = bad || !(r0 == s0 && fabsf(s0) <= 32768.0f && s0 != 32768.0f);
-    y[i] = static_cast<int16_t>(static_cast<int32_t>(r0));
+  for (; i < n8; i += stride) {
+    const float4 a = __ldcs(x4 + 2 * i), c = __ldcs(x4 + 2 * i + 1);
+    *reinterpret_cast<uint4*>(y + 8 * i) = make_uint4(pcm_f32_pair(a.x, a.y, bad), pcm_f32_pair(a.z, a.w, bad),
+                                                      pcm_f32_pair(c.x, c.y, bad), pcm_f32_pair(c.z, c.w, bad));
   }
-  if (__any_sync(0xffffffffu, bad) && (threadIdx.x & 31) == 0) atomicOr(flag, 1);
+  for (int64_t j = 8 * n8 + static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; j < len; j += stride) {
+    const uint32_t w = pcm_f32_pair(__ldg(x + j), 0.0f, bad);
+    y[j] = static_cast<int16_t>(w & 0xffffu);
+  }
+  if (bad) {  // one atomic per warp (the lanes that got here: some may have left through the flag poll)
+    const unsigned m = __activemask();
+    if ((threadIdx.x & 31) == static_cast<unsigned>(__ffs(m) - 1)) atomicOr(flag, 1);
+  }
 }
 
 }  // namespace b200mel

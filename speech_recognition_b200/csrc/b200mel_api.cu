@@ -60,6 +60,51 @@ cudaError_t upload(const std::vector<T>& v, T** dptr) {
   return cudaMemcpy(*dptr, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice);
 }
 
+// ---- MFCC second stage on the tensor cores (aux_kernels.cuh: mfcc_post_mma_kernel<NT, C>) ----
+struct MfccMmaArgs {
+  const float* lm; float* out; const int32_t* lengths; int64_t t_max; int Lw, H; const uint32_t* dct_image;
+  int n_masks_f, n_masks_t, sa_F, sa_T; float sa_p; const int32_t* mask_table; uint64_t seed, first_utt;
+  int32_t* status; const int32_t* gate; int gate_value; int batch, sm_count;
+};
+// 0 = set the shared-memory cap (handle creation), 1 = launch
+template <int NT, int C>
+cudaError_t mfcc_mma_do(int what, int max_smem_optin, const MfccMmaArgs& a, cudaStream_t st) {
+  auto kernel = mfcc_post_mma_kernel<NT, C>;
+  if (what == 0) return raise_smem_cap(kernel, max_smem_optin);
+  const int new_rows = kMfccMmaRows - (C == 3 ? 2 : 0);
+  const int64_t tiles = (a.t_max + new_rows - 1) / new_rows;
+  // each block takes a short run of consecutive tiles of one utterance (the DCT image is fetched once per block)
+  static const int forced = [] { const char* e = std::getenv("B200MEL_MFCC_TILES_PER_BLOCK"); return e ? std::atoi(e) : 0; }();
+  // (r2i, config 4k, us per step for 1/2/3/5/7/13 tiles per block: 191/181/179/187/186/184)
+  int64_t per_block = forced > 0 ? forced : std::max<int64_t>(1, std::min<int64_t>(3, tiles * a.batch / (16 * a.sm_count)));
+  const int64_t gx = (tiles + per_block - 1) / per_block;
+  dim3 grid(static_cast<unsigned>(gx), static_cast<unsigned>(a.batch));
+  kernel<<<grid, kMfccMmaThreads, mfcc_post_mma_smem_bytes(8 * NT), st>>>(
+      a.lm, a.out, a.lengths, a.t_max, a.Lw, a.H, a.dct_image, static_cast<int>(per_block), a.n_masks_f, a.n_masks_t,
+      a.sa_F, a.sa_T, a.sa_p, a.mask_table, a.seed, a.first_utt, a.status, a.gate, a.gate_value);
+  return cudaGetLastError();
+}
+template <int C>
+cudaError_t mfcc_mma_nt(int nt, int what, int max_smem_optin, const MfccMmaArgs& a, cudaStream_t st) {
+  switch (nt) {
+    case 1: return mfcc_mma_do<1, C>(what, max_smem_optin, a, st);
+    case 2: return mfcc_mma_do<2, C>(what, max_smem_optin, a, st);
+    case 3: return mfcc_mma_do<3, C>(what, max_smem_optin, a, st);
+    case 4: return mfcc_mma_do<4, C>(what, max_smem_optin, a, st);
+    case 5: return mfcc_mma_do<5, C>(what, max_smem_optin, a, st);
+    case 6: return mfcc_mma_do<6, C>(what, max_smem_optin, a, st);
+    case 7: return mfcc_mma_do<7, C>(what, max_smem_optin, a, st);
+    case 8: return mfcc_mma_do<8, C>(what, max_smem_optin, a, st);
+    case 9: return mfcc_mma_do<9, C>(what, max_smem_optin, a, st);
+    case 10: return mfcc_mma_do<10, C>(what, max_smem_optin, a, st);
+  }
+  return cudaErrorInvalidValue;
+}
+inline cudaError_t mfcc_mma(int n_mfcc, int C, int what, int max_smem_optin, const MfccMmaArgs& a, cudaStream_t st) {
+  return C == 3 ? mfcc_mma_nt<3>(n_mfcc / 8, what, max_smem_optin, a, st) : mfcc_mma_nt<1>(n_mfcc / 8, what, max_smem_optin, a, st);
+}
+inline bool mfcc_mma_shape_ok(int M, int n_mfcc) { return M == kMfccMmaM && n_mfcc >= 8 && n_mfcc <= 80 && n_mfcc % 8 == 0; }
+
 // Stream-ordered scratch that must be released on every path out of a function (error returns included).
 struct AsyncScratch {
   void* p = nullptr;
@@ -97,6 +142,7 @@ struct b200mel_handle {
   int* d_mel_off = nullptr;
   float* d_mel_w = nullptr;
   float* d_dct = nullptr;
+  uint32_t* d_dct_mma = nullptr;  // TF32 (hi, lo) image [2][M][pitch] of the DCT matrix (mfcc_post_mma_kernel)
   // generic kernel tiling
   int g_warps = 8, g_ft = 32, g_halo = 0, g_per_warp_floats = 0;
   size_t g_smem = 0;
@@ -260,6 +306,28 @@ int b200mel_create(const b200mel_config* config, int device, b200mel_handle** ou
       h->tc_ok = false;
     }
   }
+  if (h->tc_ok && p.cfg.audio_feature_type == B200MEL_FEATURE_MFCC && mfcc_mma_shape_ok(p.cfg.num_mel_bins, p.n_mfcc_eff)) {
+    // the DCT matrix split into TF32 (hi, lo) parts, in the shared-memory layout of mfcc_post_mma_kernel
+    const int M = p.cfg.num_mel_bins, nm = p.n_mfcc_eff, P = mfcc_mma_pitch(nm);
+    std::vector<uint32_t> img(static_cast<size_t>(2) * M * P, 0u);
+    for (int m = 0; m < M; ++m)
+      for (int c = 0; c < nm; ++c) {
+        const float d = p.dct[static_cast<size_t>(m) * nm + c];
+        const uint32_t hi = mfcc_tf32_host(d);
+        float hf;
+        std::memcpy(&hf, &hi, 4);
+        img[static_cast<size_t>(m) * P + c] = hi;
+        img[static_cast<size_t>(M + m) * P + c] = mfcc_tf32_host(d - hf);
+      }
+    MfccMmaArgs none{};
+    if (upload(img, &h->d_dct_mma) != cudaSuccess ||
+        mfcc_mma(nm, 1, 0, h->max_smem_optin, none, nullptr) != cudaSuccess ||
+        mfcc_mma(nm, 3, 0, h->max_smem_optin, none, nullptr) != cudaSuccess) {
+      cudaGetLastError();
+      cudaFree(h->d_dct_mma);
+      h->d_dct_mma = nullptr;  // (the scalar second stage stays available)
+    }
+  }
 #endif
   *out_handle = h;
   return B200MEL_OK;
@@ -276,6 +344,7 @@ int b200mel_destroy(b200mel_handle* h) {
   cudaFree(h->d_mel_off);
   cudaFree(h->d_mel_w);
   cudaFree(h->d_dct);
+  cudaFree(h->d_dct_mma);
   for (auto& sl : h->slots) {
     cudaFree(sl.s_pcm);
     cudaFree(sl.s_out);
@@ -441,7 +510,8 @@ int b200mel_forward(b200mel_handle* h, const void* pcm, int32_t pcm_dtype, const
     int16_t* pcm16 = reinterpret_cast<int16_t*>(static_cast<char*>(f32_scratch) + 64);
     CU_CHECK(cudaMemsetAsync(flag, 0, sizeof(int32_t), st));
     const int64_t per_row_threads = (row_stride + 7) / 8;
-    dim3 cgrid(static_cast<unsigned>(std::min<int64_t>(64, (per_row_threads + 255) / 256)), static_cast<unsigned>(batch));
+    // (four groups of eight samples per thread and round: 1024 groups per block-round)
+    dim3 cgrid(static_cast<unsigned>(std::min<int64_t>(16, (per_row_threads + 1023) / 1024)), static_cast<unsigned>(batch));
     pcm_f32_to_i16_kernel<<<cgrid, 256, 0, st>>>(static_cast<const float*>(pcm), lengths, row_stride, pcm16, flag);
     h->launches.fetch_add(1);
     kp.pcm = pcm16;
@@ -491,11 +561,18 @@ int b200mel_forward(b200mel_handle* h, const void* pcm, int32_t pcm_dtype, const
     h->launches.fetch_add(n_launched);
     if (two_stage) {
       if (rc == 0) {
-        dim3 grid(static_cast<unsigned>((t_max + kMfccFrames - 1) / kMfccFrames), static_cast<unsigned>(batch));
-        mfcc_post_kernel<<<grid, kMfccThreads, mfcc_post_smem_bytes(kp.M, kp.n_mfcc), st>>>(
-            lm, out, lengths, t_max, kp.Lw, kp.H, kp.M, kp.n_mfcc, kp.C, kp.dct, kp.n_masks_f, kp.n_masks_t, kp.sa_F,
-            kp.sa_T, kp.sa_p, mask_table, seed, first_utterance_id, status, kp.gate, kp.gate_value);
-        if (cudaGetLastError() != cudaSuccess) rc = 1;
+        if (h->d_dct_mma && (reinterpret_cast<uintptr_t>(out) & 31) == 0) {
+          const MfccMmaArgs a{lm, out, lengths, t_max, kp.Lw, kp.H, h->d_dct_mma, kp.n_masks_f, kp.n_masks_t, kp.sa_F,
+                              kp.sa_T, kp.sa_p, mask_table, seed, first_utterance_id, status, kp.gate, kp.gate_value,
+                              batch, h->sm_count};
+          if (mfcc_mma(kp.n_mfcc, kp.C, 1, h->max_smem_optin, a, st) != cudaSuccess) rc = 1;
+        } else {
+          dim3 grid(static_cast<unsigned>((t_max + kMfccFrames - 1) / kMfccFrames), static_cast<unsigned>(batch));
+          mfcc_post_kernel<<<grid, kMfccThreads, mfcc_post_smem_bytes(kp.M, kp.n_mfcc), st>>>(
+              lm, out, lengths, t_max, kp.Lw, kp.H, kp.M, kp.n_mfcc, kp.C, kp.dct, kp.n_masks_f, kp.n_masks_t, kp.sa_F,
+              kp.sa_T, kp.sa_p, mask_table, seed, first_utterance_id, status, kp.gate, kp.gate_value);
+          if (cudaGetLastError() != cudaSuccess) rc = 1;
+        }
         h->launches.fetch_add(1);
       }
       cudaFreeAsync(lm, st);
