@@ -89,8 +89,23 @@ out_h, nf_h = fe.forward_host(x[:32], lengths=lengths[:32])
 assert np.array_equal(out_h, b[:32].cpu().numpy())
 ok("forward_host")
 
-t_nf = fe(pcm[:24], lengths=len_d[:24])[1]
-nf = t_nf
+# no-alloc entry
+import ctypes                                                             # noqa: E402
+from speech_recognition_b200 import _lib                                  # noqa: E402
+
+lib = _lib.load()
+out = torch.empty((24, t_max, 40, 3), dtype=torch.float32, device=dev)
+nf = torch.empty(24, dtype=torch.int32, device=dev)
+st = torch.zeros(1, dtype=torch.int32, device=dev)
+want, _ = fe_m(pcm[:24], lengths=len_d[:24], seed=43, first_utterance_id=7, kernel="tc")
+rc = lib.b200mel_forward_mfcc_noalloc(fe_m._handle, ctypes.c_void_p(pcm.data_ptr()), None, ctypes.c_void_p(len_d.data_ptr()),
+                                      24, L, ctypes.c_void_p(out.data_ptr()), t_max, ctypes.c_void_p(nf.data_ptr()), None,
+                                      43, 7, ctypes.c_void_p(st.data_ptr()),
+                                      ctypes.c_void_p(torch.cuda.current_stream().cuda_stream))
+assert rc == 0, lib.b200mel_last_error()
+assert torch.equal(out, want)
+ok("b200mel_forward_mfcc_noalloc")
+
 # stand-alone stages and the rows either side of the path
 from speech_recognition_b200 import frontend as F_                        # noqa: E402
 

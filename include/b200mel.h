@@ -157,6 +157,28 @@ int b200mel_forward_host_submit(b200mel_handle* handle, const void* pcm_host, in
 int b200mel_forward_host_wait(b200mel_handle* handle, int32_t slot);
 
 /*
+ * No counterpart in the reference: added for callers that
+ * cannot allocate device memory inside the call (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  The MFCC path of b200mel_forward (int16 PCM, tensor-core log-mel stage ->
+ * DCT / SpecAugment / delta stage) with the intermediate log-mel tensor in a file-scope device array of
+ * B200MEL_NOALLOC_SCRATCH_BYTES instead of pool memory: the call allocates and frees nothing.
+ *   - `handle` must be an MFCC configuration for which b200mel_tc_supported() is 1 (the array's
+ *     address is resolved once per device in b200mel_create).
+ *   - batch * t_max * num_mel_bins * 4 bytes must fit the array (16 MiB: 52428 frames of 80 mel bins,
+ *     about 524 s of audio per call); larger calls return B200MEL_ERR_UNSUPPORTED.
+ *   - `out` must be 32-byte aligned.  Other arguments as in b200mel_forward.
+ *   - every call on a device shares the one array: calls that overlap on the GPU (different streams,
+ *     or different handles / threads without ordering between them) race.  Nothing in the array has to
+ *     start at zero: the first stage rewrites every row it later reads.
+ */
+#define B200MEL_NOALLOC_SCRATCH_BYTES (16u << 20)
+int b200mel_forward_mfcc_noalloc(b200mel_handle* handle, const int16_t* pcm, const int64_t* offsets,
+                                 const int32_t* lengths, int32_t batch, int64_t row_stride, float* out,
+                                 int64_t t_max, int32_t* n_frames, const int32_t* mask_table,
+                                 uint64_t seed, uint64_t first_utterance_id, int32_t* status,
+                                 void* stream);
+
+/*
  * Stand-alone stages, for callers that compose the reference's per-example maps one by one
  * (run/train.py:88-116) instead of using the fused call.
  */

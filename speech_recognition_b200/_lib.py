@@ -62,6 +62,9 @@ SIGNATURES = {
     "b200mel_forward_host_submit": (_c.c_int, [_vp, _vp, _i32, _vp, _vp, _i32, _i64, _i64, _vp, _i64, _vp, _u64,
                                                _u64, _i32, _i32]),
     "b200mel_forward_host_wait": (_c.c_int, [_vp, _i32]),
+    # (no allocation inside the call; no counterpart in the reference - see include/b200mel.h)
+    "b200mel_forward_mfcc_noalloc": (_c.c_int, [_vp, _vp, _vp, _vp, _i32, _i64, _vp, _i64, _vp, _vp, _u64, _u64,
+                                                _vp, _vp]),
     "b200mel_specaug_draw": (_c.c_int, [_vp, _i32, _i32, _i32, _i32, _i32, _c.c_float, _i32, _u64, _u64,
                                         _vp, _vp, _vp]),
     "b200mel_specaug_apply": (_c.c_int, [_vp, _vp, _i32, _i64, _i32, _i32, _vp, _i32, _i32, _vp]),

@@ -142,6 +142,7 @@ struct b200mel_handle {
   int* d_mel_off = nullptr;
   float* d_mel_w = nullptr;
   float* d_dct = nullptr;
+  float* d_noalloc_logmel = nullptr;  // device address of g_noalloc_logmel on this handle's device (b200mel_forward_mfcc_noalloc)
   uint32_t* d_dct_mma = nullptr;  // TF32 (hi, lo) image [2][M][pitch] of the DCT matrix (mfcc_post_mma_kernel)
   // generic kernel tiling
   int g_warps = 8, g_ft = 32, g_halo = 0, g_per_warp_floats = 0;
@@ -182,6 +183,8 @@ extern "C" {
 int b200mel_version(void) { return B200MEL_VERSION; }
 
 const char* b200mel_last_error(void) { return g_last_error.c_str(); }
+
+static bool noalloc_resolve(int device, float** out_ptr);  // (b200mel_forward_mfcc_noalloc, below)
 
 int b200mel_create(const b200mel_config* config, int device, b200mel_handle** out_handle) {
   if (!config || !out_handle) return fail(B200MEL_ERR_INVALID_ARGUMENT, "null argument");
@@ -327,6 +330,10 @@ int b200mel_create(const b200mel_config* config, int device, b200mel_handle** ou
       cudaFree(h->d_dct_mma);
       h->d_dct_mma = nullptr;  // (the scalar second stage stays available)
     }
+  }
+  if (h->tc_ok && p.cfg.audio_feature_type == B200MEL_FEATURE_MFCC) {
+    // set-up of b200mel_forward_mfcc_noalloc: this device is current here (DeviceGuard above)
+    if (!noalloc_resolve(device, &h->d_noalloc_logmel)) h->d_noalloc_logmel = nullptr;
   }
 #endif
   *out_handle = h;
@@ -595,6 +602,123 @@ int b200mel_forward(b200mel_handle* h, const void* pcm, int32_t pcm_dtype, const
   if (e != cudaSuccess) return cuda_fail(e, "generic_frontend_kernel launch");
   h->launches.fetch_add(1);
   return B200MEL_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// b200mel_forward_mfcc_noalloc: the two-stage MFCC path of b200mel_forward with the log-mel stage in a
+// file-scope device array instead of pool memory, for callers that may not allocate (CUDA graph
+// capture, serving loops).  No counterpart in the reference.
+// The array is per device (every GPU that loads the library holds it until exit) and
+// shared by every call on that device.
+// ---------------------------------------------------------------------------------------------
+static __device__ __align__(256) float g_noalloc_logmel[B200MEL_NOALLOC_SCRATCH_BYTES / sizeof(float)];
+
+// In host code `g_noalloc_logmel` is only a stand-in for the symbol: its device address is resolved
+// once per device, with that device current (b200mel_create calls this under its DeviceGuard).
+static std::mutex g_noalloc_mu;
+static float* g_noalloc_ptr[64];
+static bool noalloc_resolve(int device, float** out_ptr) {
+  if (device < 0 || device >= 64) return false;
+  std::lock_guard<std::mutex> lock(g_noalloc_mu);
+  if (!g_noalloc_ptr[device]) {
+    float* ptr = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress(reinterpret_cast<void**>(&ptr), g_noalloc_logmel);
+    if (e != cudaSuccess || !ptr) {
+      cudaGetLastError();
+      return false;
+    }
+    g_noalloc_ptr[device] = ptr;
+  }
+  *out_ptr = g_noalloc_ptr[device];
+  return true;
+}
+
+int b200mel_forward_mfcc_noalloc(b200mel_handle* h, const int16_t* pcm, const int64_t* offsets, const int32_t* lengths,
+                                 int32_t batch, int64_t row_stride, float* out, int64_t t_max, int32_t* n_frames,
+                                 const int32_t* mask_table, uint64_t seed, uint64_t first_utterance_id, int32_t* status,
+                                 void* stream) {
+  if (!h) return fail(B200MEL_ERR_INVALID_ARGUMENT, "null handle");
+  if (batch < 0 || t_max < 0) return fail(B200MEL_ERR_INVALID_ARGUMENT, "negative batch or t_max");
+#ifdef B200MEL_WITH_TC
+  if (h->plan.cfg.audio_feature_type != B200MEL_FEATURE_MFCC || !h->tc_ok)
+    return fail(B200MEL_ERR_UNSUPPORTED,
+                "b200mel_forward_mfcc_noalloc: the handle must be an MFCC configuration the tensor-core kernel supports");
+  if (!h->d_noalloc_logmel)
+    return fail(B200MEL_ERR_CUDA, "b200mel_forward_mfcc_noalloc: the static scratch array could not be resolved on this device");
+  if (batch == 0 || t_max == 0) return B200MEL_OK;
+  if (!lengths || !pcm || !out) return fail(B200MEL_ERR_INVALID_ARGUMENT, "null buffer");
+  if (batch > 65535) return fail(B200MEL_ERR_UNSUPPORTED, "batch > 65535: split the call");
+  KernelParams kp;
+  fill_params(h, kp);
+  const int64_t max_rows = static_cast<int64_t>(B200MEL_NOALLOC_SCRATCH_BYTES / sizeof(float)) / kp.M;
+  if (t_max > max_rows || static_cast<int64_t>(batch) * t_max > max_rows) {
+    char msg[256];
+    std::snprintf(msg, sizeof(msg),
+                  "b200mel_forward_mfcc_noalloc: batch * t_max = %lld frames exceeds the static scratch (%lld frames of %d mel "
+                  "bins, %u bytes): split the batch or use b200mel_forward",
+                  static_cast<long long>(batch) * static_cast<long long>(t_max), static_cast<long long>(max_rows), kp.M,
+                  static_cast<unsigned>(B200MEL_NOALLOC_SCRATCH_BYTES));
+    return fail(B200MEL_ERR_UNSUPPORTED, msg);
+  }
+  if (kp.n_masks_f + kp.n_masks_t > 16)
+    return fail(B200MEL_ERR_INVALID_ARGUMENT, "the tensor-core kernel handles at most 16 SpecAugment masks per utterance");
+  if (reinterpret_cast<uintptr_t>(out) & 31)
+    return fail(B200MEL_ERR_INVALID_ARGUMENT, "b200mel_forward_mfcc_noalloc needs a 32-byte aligned output buffer");
+  const int64_t tiles_per_utt = (t_max + 127) / 128;
+  if (tc_max_tiles_per_launch(h->sm_count) / tiles_per_utt < 1)
+    return fail(B200MEL_ERR_UNSUPPORTED, "t_max is too large for the tensor-core kernel");
+  DeviceGuard guard(h->device);
+  if (!guard.ok) return fail(B200MEL_ERR_CUDA, "cudaSetDevice failed");
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  kp.pcm = pcm;
+  kp.offsets = offsets;
+  kp.lengths = lengths;
+  kp.row_stride = row_stride;
+  kp.pcm_is_f32 = 0;
+  kp.batch = batch;
+  kp.out = out;
+  kp.t_max = t_max;
+  kp.n_frames = n_frames;
+  kp.status = status;
+  kp.mask_table = mask_table;
+  kp.seed = seed;
+  kp.first_utt = first_utterance_id;
+  // stage 1: log-mel [batch, t_max, M] (C = 1, no masks) into the static array - every row below t_max
+  // is written (padding rows as +0.0), so nothing of the previous call's contents is read
+  float* lm = h->d_noalloc_logmel;
+  KernelParams kp1 = kp;
+  kp1.feature_type = B200MEL_FEATURE_LOG_MEL;
+  kp1.F = kp.M;
+  kp1.C = 1;
+  kp1.n_masks_f = kp1.n_masks_t = 0;
+  kp1.mask_table = nullptr;
+  kp1.out = lm;
+  int n_launched = 0;
+  const int rc = tc_launch(h->tc, kp1, h->sm_count, st, &n_launched);
+  h->launches.fetch_add(n_launched);
+  if (rc == 2) return fail(B200MEL_ERR_CUDA, "cuTensorMapEncodeTiled failed for the scratch tensor");
+  if (rc != 0) return cuda_fail(cudaGetLastError(), "tc_frontend_kernel launch");
+  // stage 2: DCT, masks on the coefficients, deltas
+  if (h->d_dct_mma) {
+    const MfccMmaArgs a{lm, out, lengths, t_max, kp.Lw, kp.H, h->d_dct_mma, kp.n_masks_f, kp.n_masks_t, kp.sa_F,
+                        kp.sa_T, kp.sa_p, mask_table, seed, first_utterance_id, status, nullptr, 0, batch, h->sm_count};
+    const cudaError_t e = mfcc_mma(kp.n_mfcc, kp.C, 1, h->max_smem_optin, a, st);
+    if (e != cudaSuccess) return cuda_fail(e, "mfcc_post_mma_kernel launch");
+  } else {
+    dim3 grid(static_cast<unsigned>((t_max + kMfccFrames - 1) / kMfccFrames), static_cast<unsigned>(batch));
+    mfcc_post_kernel<<<grid, kMfccThreads, mfcc_post_smem_bytes(kp.M, kp.n_mfcc), st>>>(
+        lm, out, lengths, t_max, kp.Lw, kp.H, kp.M, kp.n_mfcc, kp.C, kp.dct, kp.n_masks_f, kp.n_masks_t, kp.sa_F, kp.sa_T,
+        kp.sa_p, mask_table, seed, first_utterance_id, status, nullptr, 0);
+    const cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return cuda_fail(e, "mfcc_post_kernel launch");
+  }
+  h->launches.fetch_add(1);
+  return B200MEL_OK;
+#else
+  (void)pcm; (void)offsets; (void)lengths; (void)row_stride; (void)out; (void)n_frames; (void)mask_table; (void)seed;
+  (void)first_utterance_id; (void)status; (void)stream;
+  return fail(B200MEL_ERR_UNSUPPORTED, "built without the tensor-core kernel");
+#endif
 }
 
 static int host_wait_locked(b200mel_handle* h, int slot) {
