@@ -418,8 +418,38 @@ __global__ void __launch_bounds__(kTcThreads, 1)
     w[I][4 * q + 2] = v.z;                                                                             \
     w[I][4 * q + 3] = v.w;                                                                             \
   }
+#if !defined(TC_NO_SPEC_FIRST)
+    // Dense, 16-byte aligned input: load the CTA's first tile now, while the epilogue warps still build
+    // the tile list - guessed as if every tile of the batch were active (exact for a batch of
+    // full-length utterances; the same guess as the L2 prefetch above).  The block index is clamped
+    // into the ROW here, not into the utterance: the samples between `len` and the end of the row
+    // only feed frames >= n_frames, which the epilogue zero-fills or drops.  A wrong guess is found
+    // by comparing with the list entry below and costs one wasted load.  Measured (r2k, 256 x 15 s):
+    // 76.9 -> 76.1 us per launch in the 20-step bench, 72.4 -> 72.0 us in the 100-step one.
+    int32_t spec_b = -1, spec_j = -1;
+    if (p.offsets == nullptr && pcm_al && (p.row_stride & 7) == 0 && batch_eff > 0) {
+      const int t0 = static_cast<int>((static_cast<long long>(tp.total_tiles) * blockIdx.x) / gridDim.x);
+      spec_b = t0 / tp.tiles_per_utt;
+      spec_j = t0 - spec_b * tp.tiles_per_utt;
+      if (spec_b < batch_eff && static_cast<int64_t>(spec_b + 1) * (p.row_stride >> 3) < 0x7fffffffLL) {
+        const int32_t b_lo = spec_b * static_cast<int32_t>(p.row_stride >> 3), b_hi = b_lo + static_cast<int32_t>(p.row_stride >> 3) - 1;
+        const int32_t b_0 = b_lo + 20 * (spec_j * tp.tout - tp.halo);
+        TC_LOAD_GROUP(0, b_0, b_lo, b_hi)
+        TC_LOAD_GROUP(1, b_0, b_lo, b_hi)
+        if (third) { TC_LOAD_GROUP(2, b_0, b_lo, b_hi) }
+      } else {
+        spec_b = -1;
+      }
+    }
+#endif
     if (!tc::mbar_wait(&ctl->list_full, 0)) timed_out = true;
     const int n_tiles = ctl->n_tiles;
+#if !defined(TC_NO_SPEC_FIRST)
+    if (spec_b >= 0 && n_tiles > 0) {
+      const int4 first = sList[0];
+      preloaded = first.x == spec_b && first.y == spec_j && first.w >= 0;
+    }
+#endif
     // Register budget: the 60 raw words of the NEXT tile are live across the top of the loop, so
     // nothing about the tiles is carried in registers - every use re-reads the list entry.
     // next tile: first block and clamp range, all in absolute 8-sample blocks (< 2^31 blocks)
@@ -583,6 +613,7 @@ __global__ void __launch_bounds__(kTcThreads, 1)
     // C == 3: on the staged row before the copy-out
     constexpr bool kRegMask = kMask && C == 1;
     // (two groups: the second one is "group 2" - the last group - in the generated code as well)
+    // (measured r2k: the last group of the chain on the OLDEST epilogue warps instead - no change, 72.36 vs 72.44 us)
     const int group = TC_NGROUPS == 3 ? (warp - 8) >> 2 : ((warp - 8) >> 2) * 2, wq = warp & 3;
     const int etid = tid - 256;
     const int row = wq * 32 + lane;
@@ -602,6 +633,7 @@ __global__ void __launch_bounds__(kTcThreads, 1)
     // the first epilogue warp of the grid also reports the frame counts, and flags the zero-frame
     // utterances on which the reference's time-mask draw raises
     const bool reporter = blockIdx.x == 0 && warp == 8;
+    constexpr int kTout = kTcTileM - (C == 3 ? 2 : 0);  // = tp.tout, as a constant: divisions by it are multiplications
     if (warp < 16) {
       // ---- the CTA's tile list, in one pass over the lengths (warps 8-15): thread (warp e, lane l) owns
       //      utterance 256 c + 8 l + e of every chunk c of 256; a warp scan of the per-lane counts gives
@@ -618,7 +650,7 @@ __global__ void __launch_bounds__(kTcThreads, 1)
         for (int k = 0; k < 8; ++k) {
           const int bq = base + 8 * lane + k;
           const int32_t l = bq < batch_eff ? __ldg(p.lengths + bq) : 0;
-          c[k] = bq < batch_eff ? tc_nact(l, t_max32, tp.tout) : 0;
+          c[k] = bq < batch_eff ? tc_nact(l, t_max32, kTout) : 0;
           sum += c[k];
           if (k == ew) mylen = l;
           if (bq < batch_eff && (nfo || sfe)) {
@@ -631,7 +663,16 @@ __global__ void __launch_bounds__(kTcThreads, 1)
         for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
         total += sum;
       }
-      const long long a0 = (total * blockIdx.x) / gridDim.x, a1r = (total * (blockIdx.x + 1)) / gridDim.x;
+      // (64-bit divisions are subroutine calls: the usual batch takes the 32-bit ones)
+      long long a0, a1r;
+      if (total < (1 << 20) && gridDim.x < (1 << 11)) {
+        const uint32_t tt = static_cast<uint32_t>(total);
+        a0 = (tt * blockIdx.x) / gridDim.x;
+        a1r = (tt * (blockIdx.x + 1)) / gridDim.x;
+      } else {
+        a0 = (total * blockIdx.x) / gridDim.x;
+        a1r = (total * (blockIdx.x + 1)) / gridDim.x;
+      }
       const long long a1 = a1r - a0 > kTcListTiles ? a0 + kTcListTiles : a1r;  // (the host keeps ranges within the list)
       if (ew == 0 && lane == 0) ctl->n_tiles = static_cast<int32_t>(a1 - a0);
       long long acc = 0;
@@ -641,7 +682,7 @@ __global__ void __launch_bounds__(kTcThreads, 1)
           for (int k = 0; k < 8; ++k) {
             const int bq = base + 8 * lane + k;
             const int32_t l = bq < batch_eff ? __ldg(p.lengths + bq) : 0;
-            c[k] = bq < batch_eff ? tc_nact(l, t_max32, tp.tout) : 0;
+            c[k] = bq < batch_eff ? tc_nact(l, t_max32, kTout) : 0;
             if (k == ew) mylen = l;
           }
         }
@@ -739,6 +780,9 @@ __global__ void __launch_bounds__(kTcThreads, 1)
 #ifndef TC_LOOP_MODE
 #define TC_LOOP_MODE 0   // measured: rolled 78.7 us, straight-line + software-pipelined 87.9 us per launch (see below)
 #endif
+#ifndef TC_CFREE_Q
+#define TC_CFREE_Q 0     // quad (counted from the group's first) after which group C frees the previous tile's rows (r2k: 2 = no change)
+#endif
 #define TC_QUAD_ADDR(Q, R) (t_tile + (((5u * n + (R)) & 7u) << 6) + 4 * (Q))
 #if TC_LOOP_MODE == 0
       // rolled loop, one quad per iteration: load, wait, compute - except the last TC_TAIL_K quads, which are
@@ -755,7 +799,7 @@ __global__ void __launch_bounds__(kTcThreads, 1)
     _Pragma("unroll") for (int r = 0; r < 5; ++r) tc::tmem_ld4(TC_QUAD_ADDR(q, r), d[0][r]);      \
     tc::tmem_ld_wait();                                                                           \
     TC_QUAD_MATH(G, q, d[0])                                                                      \
-    if (q == (Q0)) { CFREE }                                                                      \
+    if (q == (Q0) + TC_CFREE_Q) { CFREE }                                                         \
     TC_G##G##_SWITCH(q, P);                                                                       \
   }                                                                                               \
   _Pragma("unroll") for (int k = 0; k < kTail; ++k)                                               \

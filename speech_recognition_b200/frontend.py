@@ -99,13 +99,13 @@ class FeatureFrontend:
                    spec_augment=sa, device=device)
 
     def __del__(self):
-        h = getattr(self, "_handle", None)
-        if h is not None and h.value:
-            try:
+        try:   # (at interpreter shutdown the module globals may already be gone)
+            h = getattr(self, "_handle", None)
+            if h is not None and h.value:
+                self._handle = None
                 _lib.load().b200mel_destroy(h)
-            except Exception:
-                pass
-            self._handle = ctypes.c_void_p()
+        except Exception:
+            pass
 
     # ------------------------------------------------------------------------------------------
     def num_frames(self, n_samples: int) -> int:
@@ -238,6 +238,67 @@ class FeatureFrontend:
         if return_status:
             return out, n_frames, status
         return out, n_frames
+
+    # ------------------------------------------------------------------------------------------
+    def bind(self, pcm: torch.Tensor, lengths: torch.Tensor, out: torch.Tensor, n_frames: torch.Tensor,
+             offsets: Optional[torch.Tensor] = None, seed: int = 0, first_utterance_id: int = 0,
+             mask_table: Optional[torch.Tensor] = None, status: Optional[torch.Tensor] = None,
+             kernel: str = "auto", stream: Optional[torch.cuda.Stream] = None):
+        """Steady-state form of ``__call__`` for a loop that reuses its buffers (a training input pipeline
+        does): every argument is a device tensor, checked ONCE here; the returned zero-argument callable
+        only makes the C call (``b200mel_forward`` with the same pointers), on ``stream`` (default: the
+        torch stream current at bind time).  Host cost per step: the ctypes call + the launch (~5 us)
+        instead of ~17 us of argument handling - that matters when the kernel is 75 us and the timed
+        region starts on an idle GPU.  The callable keeps the tensors alive; results land in ``out`` /
+        ``n_frames`` (and ``status``, OR-ed, when given) exactly as with ``__call__``."""
+        if kernel not in _lib.KERNELS:
+            raise ValueError("kernel must be one of %s" % sorted(_lib.KERNELS))
+        for name, t, dt in (("pcm", pcm, None), ("lengths", lengths, torch.int32), ("out", out, torch.float32),
+                            ("n_frames", n_frames, torch.int32), ("offsets", offsets, torch.int64),
+                            ("mask_table", mask_table, torch.int32), ("status", status, torch.int32)):
+            if t is None:
+                if name in ("offsets", "mask_table", "status"):
+                    continue
+                raise ValueError("%s is required" % name)
+            if not t.is_cuda or t.device != self.device or not t.is_contiguous():
+                raise ValueError("%s must be a contiguous tensor on %s" % (name, self.device))
+            if dt is not None and t.dtype != dt:
+                raise ValueError("%s must be %s" % (name, dt))
+        if pcm.dtype == torch.int16:
+            dt = _lib.PCM_I16
+        elif pcm.dtype == torch.float32:
+            dt = _lib.PCM_F32
+        else:
+            raise ValueError("pcm must be int16 or float32, got %s" % pcm.dtype)
+        if offsets is None:
+            if pcm.dim() != 2:
+                raise ValueError("dense pcm must be [B, L]")
+            B, row_stride = int(pcm.shape[0]), int(pcm.shape[1])
+        else:
+            if pcm.dim() != 1:
+                raise ValueError("ragged pcm must be 1-D")
+            B, row_stride = int(offsets.shape[0]), 0
+        F, C = self.frequency_dim, self.feature_dim
+        if out.dim() != 4 or out.shape[0] != B or out.shape[2] != F or out.shape[3] != C:
+            raise ValueError("out must be [B, t_max, %d, %d]" % (F, C))
+        t_max = int(out.shape[1])
+        if lengths.shape != (B,) or n_frames.shape != (B,):
+            raise ValueError("lengths and n_frames must have shape [B]")
+        if mask_table is not None and mask_table.shape != (B, 2 * (self.num_freq_masks + self.num_time_masks)):
+            raise ValueError("mask_table must be int32 [B, %d]" % (2 * (self.num_freq_masks + self.num_time_masks)))
+        st = stream if stream is not None else torch.cuda.current_stream(self.device)
+        args = (self._handle, _ptr(pcm), dt, _ptr(offsets), _ptr(lengths), B, row_stride, _ptr(out), t_max,
+                _ptr(n_frames), _ptr(mask_table), seed & 0xFFFFFFFFFFFFFFFF, first_utterance_id & 0xFFFFFFFFFFFFFFFF,
+                _ptr(status), _lib.KERNELS[kernel], ctypes.c_void_p(st.cuda_stream))
+        keep = (pcm, lengths, out, n_frames, offsets, mask_table, status, st)
+        fwd, check = self._forward, _lib.check
+
+        def bound_step(_args=args, _keep=keep):
+            rc = fwd(*_args)
+            if rc:
+                check(rc)
+
+        return bound_step
 
     # ------------------------------------------------------------------------------------------
     def forward_host(self, pcm, lengths=None, offsets=None, t_max: Optional[int] = None, seed: int = 0,
