@@ -54,7 +54,7 @@ SEED = 43                                                              # train_c
 B, SECONDS, SR = 256, 15, 16000
 L = SECONDS * SR                       # 240000 samples
 T = 1 + (L - 320) // 160               # 1499 frames
-SPIN_UP_MS = 0.0                       # (--spin-up-ms) default off: see the note at its use
+SPIN_UP_MS = 8.0                       # (--spin-up-ms) untimed passes before the W warm-up steps: see the note at its use
 RING = 5                               # distinct batches cycled through: 5 x 245.7 MB >> 126 MB L2
 
 CONFIGS = {

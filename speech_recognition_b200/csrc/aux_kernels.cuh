@@ -4,6 +4,8 @@
 
 #include <cstring>
 
+#include <cuda_fp16.h>
+
 #include "common.cuh"
 
 namespace b200mel {
@@ -247,46 +249,64 @@ __global__ void __launch_bounds__(kMfccThreads)
 }
 
 // ---------------------------------------------------------------------------------------------
-// The same second stage with the DCT on the tensor cores (mma.sync m16n8k8, TF32 operands, float32
+// The same second stage with the DCT on the tensor cores (mma.sync m16n8k16, f16 operands, float32
 // accumulators) for the shipped shape M = 80 and n_mfcc a multiple of 8 (kspon / clovacall: 40).
-// Float32 accuracy comes from the usual three-product split: x = xh + xl, d = dh + dl with every part
-// a TF32 number, x d ~ xl dh + xh dl + xh dh (the dropped xl dl term is 2^-22 relative).  The DCT
-// image (dh, dl) is split once on the host (b200mel_create) and copied as it is; the log-mel operand is
-// split in registers.  One block = 128 threads, tiles of 64 rows (warp w owns rows 16 w .. 16 w + 15),
-// `tiles_per_block` consecutive tiles of one utterance per block so that the DCT image and the mask
-// table are fetched once.  With deltas a tile recomputes the 2 rows before it (62 new rows per tile).
-// Copy-out items are (row, 8 coefficients): 32 bytes (C = 1) or 96 bytes (C = 3) of whole sectors,
+// Float32-class accuracy comes from the usual three-product split: x = xh + xl, d = dh + dl with every
+// part an f16 number (|log-mel| < 32 and |d| < 0.08: both parts are normal f16 numbers or harmlessly
+// small), x d ~ xl dh + xh dl + xh dh; the dropped xl dl term and the roundings of xl, dl stay below
+// 1e-4 on a coefficient in the worst case (measured against the oracle: DESIGN.md 4.1b).  The DCT image
+// (dh, dl) is split once on the host (b200mel_create); the log-mel operand is split in registers.
+//   One block = 256 threads, tiles of 128 rows (warp w owns rows 16 w .. 16 w + 15; with deltas a tile
+// recomputes the 2 rows before it: 126 new rows).  The batch's tiles, in one flat utterance-major index,
+// are cut into one contiguous run per block of a single resident wave (3 blocks per SM).
+//   The log-mel rows never pass through shared memory: a lane reads its A fragments straight from HBM
+// / L2 with 128-bit loads (the next tile's rows are pulled into L2 one tile ahead).  The order of the
+// products inside a dot product is free, so the k index of the fragments is permuted to make that
+// possible: lane (g, tq) loads x[16 j + 4 tq .. + 3] (j = 0..4) of rows g and g + 8 - whole 64-byte runs
+// per quad, every sector used once - and uses the four values as fragment columns 2 tq, 2 tq + 1,
+// 2 tq + 8, 2 tq + 9 of k-step j.  The host stores the image in the same order, one 16-byte entry
+// (b0 hi, b1 hi, b0 lo, b1 lo) per (k-step, tq, coefficient): one 128-bit load per fragment.
+//   Copy-out items are (row, 8 coefficients): 32 bytes (C = 1) or 96 bytes (C = 3) of whole sectors,
 // written with 256-bit stores: `out` must be 32-byte aligned.
-// Pitches: log-mel rows 84 floats (A fragments: bank 20 g + t, conflict-free), DCT rows and coefficient
-// rows P = mfcc_mma_pitch(n_mfcc) with P mod 32 in {8, 24} (B fragments: bank 8 t + g).
+//   History (256 x 15 s, MFCC-40 + delta, second stage alone): TF32 m16n8k8, rows staged in shared
+// memory, 64-row tiles 105 us; fragments from global memory, 128-row tiles 88 us; one resident wave + L2
+// prefetch 82 us; next tile in a second register set at two blocks per SM 95 us; warp-private 16-row
+// units without block barriers 93 us (14 % more MMAs for the recomputed rows - the time follows the MMA
+// count: the kernel is bound by the legacy tensor path, ~160 TF32 MAC per clock and SM); f16 m16n8k16
+// (half the instructions, twice the MACs each): see DESIGN.
 // ---------------------------------------------------------------------------------------------
-constexpr int kMfccMmaRows = 64, kMfccMmaThreads = 128, kMfccMmaM = 80, kMfccMmaPitchX = 84;
-__host__ __device__ constexpr int mfcc_mma_pitch(int n_mfcc) {
+constexpr int kMfccMmaRows = 128, kMfccMmaThreads = 256, kMfccMmaM = 80;
+__host__ __device__ constexpr int mfcc_mma_pitch(int n_mfcc) {   // coefficient rows in shared memory (floats)
   int p = n_mfcc;
   while ((p & 31) != 8 && (p & 31) != 24) ++p;
   return p;
 }
+// image entries per (k-step, tq) row: 128-bit loads of lanes (g, tq) are conflict-free when PN mod 8 == 2
+__host__ __device__ constexpr int mfcc_mma_image_pitch(int n_mfcc) {
+  int p = n_mfcc;
+  while ((p & 7) != 2) ++p;
+  return p;
+}
+// mel bin multiplied by fragment column s (0..15) of k-step j for lane-quad column tq = (s & 7) >> 1
+__host__ __device__ constexpr int mfcc_mma_image_k(int j, int s) {
+  return 16 * j + 4 * ((s & 7) >> 1) + 2 * (s >> 3) + (s & 1);
+}
+inline size_t mfcc_mma_image_words(int n_mfcc) { return static_cast<size_t>(kMfccMmaM / 16) * 4 * mfcc_mma_image_pitch(n_mfcc) * 4; }
 inline size_t mfcc_post_mma_smem_bytes(int n_mfcc) {
-  const int P = mfcc_mma_pitch(n_mfcc);
-  const int x_floats = kMfccMmaRows * (kMfccMmaPitchX > P ? kMfccMmaPitchX : P);
-  return sizeof(float) * (static_cast<size_t>(x_floats) + 2u * kMfccMmaM * P);
+  return sizeof(float) * (static_cast<size_t>(kMfccMmaRows) * mfcc_mma_pitch(n_mfcc) + mfcc_mma_image_words(n_mfcc));
 }
-// round-to-nearest (ties away) TF32 of a float, as bits: the host-side twin of cvt.rna.tf32.f32
-inline uint32_t mfcc_tf32_host(float x) {
-  uint32_t u;
-  std::memcpy(&u, &x, 4);
-  u = (u + 0x1000u) & 0xffffe000u;
-  return u;
-}
-__device__ __forceinline__ uint32_t mfcc_tf32(float x) {
-  uint32_t r;
-  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
-  return r;
-}
-__device__ __forceinline__ void mfcc_mma_tf32(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
-  asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+__device__ __forceinline__ void mfcc_mma_f16(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+  asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
                : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
                : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+// (x0, x1) -> packed f16 pairs: hi = rn(x), lo = rn(x - hi)
+__device__ __forceinline__ void mfcc_split_f16(float x0, float x1, uint32_t& hi, uint32_t& lo) {
+  const __half2 h = __floats2half2_rn(x0, x1);
+  const float2 hf = __half22float2(h);
+  const __half2 l = __floats2half2_rn(x0 - hf.x, x1 - hf.y);
+  hi = *reinterpret_cast<const uint32_t*>(&h);
+  lo = *reinterpret_cast<const uint32_t*>(&l);
 }
 __device__ __forceinline__ void mfcc_st_v8(float* p, const float* v) {
   asm volatile("st.global.v8.f32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(p), "f"(v[0]), "f"(v[1]), "f"(v[2]),
@@ -295,44 +315,57 @@ __device__ __forceinline__ void mfcc_st_v8(float* p, const float* v) {
 }
 
 template <int NT, int C>
-__global__ void __launch_bounds__(kMfccMmaThreads)
+__global__ void __launch_bounds__(kMfccMmaThreads, 3)
     mfcc_post_mma_kernel(const float* __restrict__ lm, float* __restrict__ out, const int32_t* __restrict__ lengths,
-                         int64_t t_max, int Lw, int H, const uint32_t* __restrict__ dct_image, int tiles_per_block,
+                         int batch, int64_t t_max, int Lw, int H, const uint32_t* __restrict__ dct_image, int reverse,
                          int n_masks_f, int n_masks_t, int sa_F, int sa_T, float sa_p,
                          const int32_t* __restrict__ mask_table, uint64_t seed, uint64_t first_utt, int32_t* status,
                          const int32_t* __restrict__ gate, int gate_value) {
   extern __shared__ __align__(16) float mfcc_smem[];
   if (gate && (*gate != 0) != (gate_value != 0)) return;
-  constexpr int M = kMfccMmaM, n_mfcc = 8 * NT, P = mfcc_mma_pitch(n_mfcc), PX = kMfccMmaPitchX;
+  constexpr int M = kMfccMmaM, n_mfcc = 8 * NT, P = mfcc_mma_pitch(n_mfcc), PN = mfcc_mma_image_pitch(n_mfcc);
   constexpr int halo = C == 3 ? 2 : 0, new_rows = kMfccMmaRows - halo;
-  constexpr int x_floats = kMfccMmaRows * (PX > P ? PX : P);
-  float* sx = mfcc_smem;                                          // [64][PX] log-mel rows, then [64][P] coefficients
-  uint32_t* sd = reinterpret_cast<uint32_t*>(mfcc_smem + x_floats);  // [2][M][P] TF32 (hi, lo) of the DCT matrix
+  constexpr int kImageVec = (M / 16) * 4 * PN;                                // 16-byte entries of the image
+  float* sc = mfcc_smem;                                                      // [128][P] coefficient rows of the tile
+  const uint4* sd = reinterpret_cast<const uint4*>(mfcc_smem + kMfccMmaRows * P);  // [5][4][PN] (b0 hi, b1 hi, b0 lo, b1 lo)
   __shared__ int32_t s_table[2 * kMaxMasks];
-  const int b = blockIdx.y;
-  const int64_t n_tiles = (t_max + new_rows - 1) / new_rows;
-  const int64_t tile0 = static_cast<int64_t>(blockIdx.x) * tiles_per_block;
-  if (tile0 >= n_tiles) return;
-  const int64_t tile1 = tile0 + tiles_per_block < n_tiles ? tile0 + tiles_per_block : n_tiles;
-  const int32_t n_fr_all = frames_of(lengths[b], Lw, H);
-  const int64_t n_fr = n_fr_all < t_max ? n_fr_all : t_max;
+  // Work: the batch's tiles in one flat index (utterance-major), cut into gridDim.x contiguous runs - one
+  // resident wave of blocks, no tail wave; `reverse` walks the index from the end.
+  const int64_t tiles_per_utt = (t_max + new_rows - 1) / new_rows;
+  const int64_t total = tiles_per_utt * batch;
+  const int64_t w0 = (total * blockIdx.x) / gridDim.x, w1 = (total * (blockIdx.x + 1)) / gridDim.x;
+  if (w0 >= w1) return;
+  for (int i = threadIdx.x; i < kImageVec; i += kMfccMmaThreads)
+    reinterpret_cast<uint4*>(mfcc_smem + kMfccMmaRows * P)[i] = __ldg(reinterpret_cast<const uint4*>(dct_image) + i);
   const int n_masks = n_masks_f + n_masks_t;
-  if (threadIdx.x == 0 && n_masks > 0) {
-    if (mask_table) {
-      for (int i = 0; i < 2 * n_masks; ++i) s_table[i] = mask_table[static_cast<size_t>(b) * 2 * n_masks + i];
-    } else {
-      const int bad = specaug_draw_table(n_fr_all, n_mfcc, sa_F, n_masks_f, sa_T, sa_p, n_masks_t, seed,
-                                         first_utt + static_cast<uint64_t>(b), s_table);
-      if (bad && blockIdx.x == 0 && status) atomicOr(status, 1);
-    }
-  }
-  if (tile0 * new_rows - halo < n_fr)  // (a block that only writes padding never reads the matrix)
-    for (int i = threadIdx.x; i < 2 * M * P / 4; i += kMfccMmaThreads)
-      reinterpret_cast<uint4*>(sd)[i] = __ldg(reinterpret_cast<const uint4*>(dct_image) + i);
-  const float* lmb = lm + static_cast<int64_t>(b) * t_max * M;
-  float* outb = out + static_cast<int64_t>(b) * t_max * n_mfcc * C;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, tq = lane & 3;
-  for (int64_t tile = tile0; tile < tile1; ++tile) {
+  int cur_b = -1;
+  int32_t n_fr_all = 0;
+  int64_t n_fr = 0;
+  for (int64_t w = w0; w < w1; ++w) {
+    const int64_t idx = reverse ? total - 1 - w : w;
+    const int b = static_cast<int>(idx / tiles_per_utt);
+    const int64_t tile = idx - b * tiles_per_utt;
+    if (b != cur_b) {   // (block-uniform)
+      cur_b = b;
+      n_fr_all = frames_of(lengths[b], Lw, H);
+      n_fr = n_fr_all < t_max ? n_fr_all : t_max;
+      __syncthreads();   // nobody still reads the previous utterance's table
+      if (threadIdx.x == 0 && n_masks > 0) {
+        if (mask_table) {
+          for (int i = 0; i < 2 * n_masks; ++i) s_table[i] = mask_table[static_cast<size_t>(b) * 2 * n_masks + i];
+        } else {
+          const int bad = specaug_draw_table(n_fr_all, n_mfcc, sa_F, n_masks_f, sa_T, sa_p, n_masks_t, seed,
+                                             first_utt + static_cast<uint64_t>(b), s_table);
+          // (reported once per utterance: by the block whose run holds the utterance's tile 0)
+          const int64_t i0 = static_cast<int64_t>(b) * tiles_per_utt, wt0 = reverse ? total - 1 - i0 : i0;
+          if (bad && wt0 >= w0 && wt0 < w1 && status) atomicOr(status, 1);
+        }
+      }
+      __syncthreads();   // table (and, the first time, the image) visible
+    }
+    const float* lmb = lm + static_cast<int64_t>(b) * t_max * M;
+    float* outb = out + static_cast<int64_t>(b) * t_max * n_mfcc * C;
     const int64_t t0 = tile * new_rows;                           // first row this tile writes
     const int n_rows = t_max - t0 < new_rows ? static_cast<int>(t_max - t0) : new_rows;
     if (t0 - halo >= n_fr) {
@@ -343,41 +376,50 @@ __global__ void __launch_bounds__(kMfccMmaThreads)
       for (int i = threadIdx.x; i < n8; i += kMfccMmaThreads) mfcc_st_v8(o + 8 * i, z);
       continue;
     }
-    // ---- log-mel rows t0 - halo .. t0 - halo + 63 (zero outside [0, n_fr)) ----
-    for (int i = threadIdx.x; i < kMfccMmaRows * (M / 4); i += kMfccMmaThreads) {
-      const int r = i / (M / 4), q = i - r * (M / 4);
-      const int64_t t = t0 - halo + r;
-      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (t >= 0 && t < n_fr) v = __ldg(reinterpret_cast<const float4*>(lmb + t * M) + q);
-      *reinterpret_cast<float4*>(sx + r * PX + 4 * q) = v;
+    // this lane's rows: 16 warp + g and + 8; raw log-mel values x[16 j + 4 tq .. + 3], j = 0..4
+    float4 xa[5], xb[5];
+    {
+      const int64_t ta = t0 - halo + 16 * warp + g, tb = ta + 8;
+      const bool la = ta >= 0 && ta < n_fr, lb = tb >= 0 && tb < n_fr;
+      const float4* pa = reinterpret_cast<const float4*>(lmb + ta * M) + tq;
+      const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+      for (int j = 0; j < 5; ++j) {
+        xa[j] = la ? __ldg(pa + 4 * j) : z;
+        xb[j] = lb ? __ldg(pa + 2 * M + 4 * j) : z;
+      }
     }
-    __syncthreads();
+    if (w + 1 < w1) {
+      // pull the next tile's rows into L2 (its 128 rows x 320 bytes are one contiguous range)
+      const int64_t nidx = reverse ? idx - 1 : idx + 1;
+      const int64_t nb = nidx / tiles_per_utt;
+      const int64_t nt0 = (nidx - nb * tiles_per_utt) * new_rows - halo;
+      const int64_t r0 = nt0 < 0 ? 0 : nt0, r1 = nt0 + kMfccMmaRows < t_max ? nt0 + kMfccMmaRows : t_max;
+      const float* base = lm + (nb * t_max + r0) * M;
+      const int64_t n_lines = ((r1 - r0) * M * 4 + 127) >> 7;
+      for (int64_t i = threadIdx.x; i < n_lines; i += kMfccMmaThreads) asm volatile("prefetch.global.L2 [%0];" ::"l"(base + 32 * i));
+    }
     float acc[NT][4];
 #pragma unroll
     for (int nt = 0; nt < NT; ++nt)
 #pragma unroll
       for (int i = 0; i < 4; ++i) acc[nt][i] = 0.0f;
-    const float* xa = sx + (16 * warp + g) * PX + tq;
-#pragma unroll 2
-    for (int ks = 0; ks < M / 8; ++ks) {
-      const float a[4] = {xa[8 * ks], xa[8 * ks + 8 * PX], xa[8 * ks + 4], xa[8 * ks + 8 * PX + 4]};
-      uint32_t ah[4], al[4];
 #pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        ah[i] = mfcc_tf32(a[i]);
-        al[i] = mfcc_tf32(a[i] - __uint_as_float(ah[i]));
-      }
-      const uint32_t* bh = sd + (8 * ks + tq) * P + g;
-      const uint32_t* bl = bh + M * P;
+    for (int j = 0; j < M / 16; ++j) {
+      uint32_t ah[4], al[4];   // a0 = row g cols (2tq, 2tq+1), a1 = row g+8 same, a2 = row g cols (2tq+8, +9), a3 = row g+8 same
+      mfcc_split_f16(xa[j].x, xa[j].y, ah[0], al[0]);
+      mfcc_split_f16(xb[j].x, xb[j].y, ah[1], al[1]);
+      mfcc_split_f16(xa[j].z, xa[j].w, ah[2], al[2]);
+      mfcc_split_f16(xb[j].z, xb[j].w, ah[3], al[3]);
+      const uint4* bp = sd + (4 * j + tq) * PN + g;
 #pragma unroll
       for (int nt = 0; nt < NT; ++nt) {
-        const uint32_t h0 = bh[8 * nt], h1 = bh[8 * nt + 4 * P], l0 = bl[8 * nt], l1 = bl[8 * nt + 4 * P];
-        mfcc_mma_tf32(acc[nt], al, h0, h1);
-        mfcc_mma_tf32(acc[nt], ah, l0, l1);
-        mfcc_mma_tf32(acc[nt], ah, h0, h1);
+        const uint4 bb = bp[8 * nt];   // (b0 hi, b1 hi, b0 lo, b1 lo)
+        mfcc_mma_f16(acc[nt], al, bb.x, bb.y);
+        mfcc_mma_f16(acc[nt], ah, bb.z, bb.w);
+        mfcc_mma_f16(acc[nt], ah, bb.x, bb.y);
       }
     }
-    __syncthreads();  // every read of the log-mel rows is done: the coefficients overwrite them
 #pragma unroll
     for (int half = 0; half < 2; ++half) {
       const int r = 16 * warp + g + 8 * half;
@@ -391,14 +433,14 @@ __global__ void __launch_bounds__(kMfccMmaThreads)
           v0 *= mask_value(s_table, n_masks_f, n_masks_t, static_cast<int>(t), c);
           v1 *= mask_value(s_table, n_masks_f, n_masks_t, static_cast<int>(t), c + 1);
         }
-        *reinterpret_cast<float2*>(sx + r * P + c) = make_float2(v0, v1);
+        *reinterpret_cast<float2*>(sc + r * P + c) = make_float2(v0, v1);
       }
     }
     __syncthreads();
     // ---- copy-out: item = (row, 8 coefficients) ----
     for (int i = threadIdx.x; i < n_rows * NT; i += kMfccMmaThreads) {
       const int r = i / NT, j = i - r * NT;
-      const float* x0p = sx + (r + halo) * P + 8 * j;
+      const float* x0p = sc + (r + halo) * P + 8 * j;
       float* o = outb + ((t0 + r) * n_mfcc + 8 * j) * C;
       float x0[8];
       *reinterpret_cast<float4*>(x0) = *reinterpret_cast<const float4*>(x0p);
@@ -424,7 +466,7 @@ __global__ void __launch_bounds__(kMfccMmaThreads)
         mfcc_st_v8(o + 16, y + 16);
       }
     }
-    __syncthreads();  // the next tile's rows overwrite the coefficients
+    __syncthreads();  // the next tile's coefficients overwrite these rows
   }
 }
 

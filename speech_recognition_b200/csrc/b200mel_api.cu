@@ -72,15 +72,15 @@ cudaError_t mfcc_mma_do(int what, int max_smem_optin, const MfccMmaArgs& a, cuda
   auto kernel = mfcc_post_mma_kernel<NT, C>;
   if (what == 0) return raise_smem_cap(kernel, max_smem_optin);
   const int new_rows = kMfccMmaRows - (C == 3 ? 2 : 0);
-  const int64_t tiles = (a.t_max + new_rows - 1) / new_rows;
-  // each block takes a short run of consecutive tiles of one utterance (the DCT image is fetched once per block)
-  static const int forced = [] { const char* e = std::getenv("B200MEL_MFCC_TILES_PER_BLOCK"); return e ? std::atoi(e) : 0; }();
-  // (r2i, config 4k, us per step for 1/2/3/5/7/13 tiles per block: 191/181/179/187/186/184)
-  int64_t per_block = forced > 0 ? forced : std::max<int64_t>(1, std::min<int64_t>(3, tiles * a.batch / (16 * a.sm_count)));
-  const int64_t gx = (tiles + per_block - 1) / per_block;
-  dim3 grid(static_cast<unsigned>(gx), static_cast<unsigned>(a.batch));
+  const int64_t tiles = (a.t_max + new_rows - 1) / new_rows * a.batch;
+  if (tiles <= 0) return cudaSuccess;
+  // one resident wave: three blocks per SM, each a contiguous run of the batch's tiles
+  // (walked from the end: the rows the first stage wrote last are still in L2 - r2t: 137.5 vs 138.5 us)
+  static const int rev = [] { const char* e = std::getenv("B200MEL_MFCC_REVERSE"); return e ? std::atoi(e) : 1; }();
+  const int64_t slots = 3LL * a.sm_count;
+  dim3 grid(static_cast<unsigned>(tiles < slots ? tiles : slots));
   kernel<<<grid, kMfccMmaThreads, mfcc_post_mma_smem_bytes(8 * NT), st>>>(
-      a.lm, a.out, a.lengths, a.t_max, a.Lw, a.H, a.dct_image, static_cast<int>(per_block), a.n_masks_f, a.n_masks_t,
+      a.lm, a.out, a.lengths, a.batch, a.t_max, a.Lw, a.H, a.dct_image, rev, a.n_masks_f, a.n_masks_t,
       a.sa_F, a.sa_T, a.sa_p, a.mask_table, a.seed, a.first_utt, a.status, a.gate, a.gate_value);
   return cudaGetLastError();
 }
@@ -310,18 +310,30 @@ int b200mel_create(const b200mel_config* config, int device, b200mel_handle** ou
     }
   }
   if (h->tc_ok && p.cfg.audio_feature_type == B200MEL_FEATURE_MFCC && mfcc_mma_shape_ok(p.cfg.num_mel_bins, p.n_mfcc_eff)) {
-    // the DCT matrix split into TF32 (hi, lo) parts, in the shared-memory layout of mfcc_post_mma_kernel
-    const int M = p.cfg.num_mel_bins, nm = p.n_mfcc_eff, P = mfcc_mma_pitch(nm);
-    std::vector<uint32_t> img(static_cast<size_t>(2) * M * P, 0u);
-    for (int m = 0; m < M; ++m)
-      for (int c = 0; c < nm; ++c) {
-        const float d = p.dct[static_cast<size_t>(m) * nm + c];
-        const uint32_t hi = mfcc_tf32_host(d);
-        float hf;
-        std::memcpy(&hf, &hi, 4);
-        img[static_cast<size_t>(m) * P + c] = hi;
-        img[static_cast<size_t>(M + m) * P + c] = mfcc_tf32_host(d - hf);
-      }
+    // the DCT matrix split into f16 (hi, lo) parts, in the shared-memory layout of mfcc_post_mma_kernel:
+    // entry (k-step j, tq, coefficient n) = (b0 hi, b1 hi, b0 lo, b1 lo), b0 = fragment columns (2 tq, 2 tq + 1),
+    // b1 = (2 tq + 8, 2 tq + 9), each a packed pair of halves (low half = the even column)
+    const int M = p.cfg.num_mel_bins, nm = p.n_mfcc_eff, PN = mfcc_mma_image_pitch(nm);
+    std::vector<uint32_t> img(mfcc_mma_image_words(nm), 0u);
+    auto split = [&](int k, int c, uint16_t& hi, uint16_t& lo) {
+      const float d = p.dct[static_cast<size_t>(k) * nm + c];
+      const __half h = __float2half_rn(d);
+      const __half l = __float2half_rn(d - __half2float(h));
+      std::memcpy(&hi, &h, 2);
+      std::memcpy(&lo, &l, 2);
+    };
+    for (int j = 0; j < M / 16; ++j)
+      for (int tq = 0; tq < 4; ++tq)
+        for (int c = 0; c < nm; ++c) {
+          uint32_t* e = &img[(static_cast<size_t>(4 * j + tq) * PN + c) * 4];
+          for (int part = 0; part < 2; ++part) {   // b0, b1
+            uint16_t h0, l0, h1, l1;
+            split(mfcc_mma_image_k(j, 2 * tq + 8 * part), c, h0, l0);
+            split(mfcc_mma_image_k(j, 2 * tq + 8 * part + 1), c, h1, l1);
+            e[part] = static_cast<uint32_t>(h0) | (static_cast<uint32_t>(h1) << 16);
+            e[2 + part] = static_cast<uint32_t>(l0) | (static_cast<uint32_t>(l1) << 16);
+          }
+        }
     MfccMmaArgs none{};
     if (upload(img, &h->d_dct_mma) != cudaSuccess ||
         mfcc_mma(nm, 1, 0, h->max_smem_optin, none, nullptr) != cudaSuccess ||
