@@ -277,10 +277,13 @@ int b200mel_create(const b200mel_config* config, int device, b200mel_handle** ou
   }
   if (h->tc_ok) {
     // per-device function attribute: set it while this handle's device is current
-    if (cudaFuncSetAttribute(tc_frontend_kernel<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmemTotal) != cudaSuccess ||
-        cudaFuncSetAttribute(tc_frontend_kernel<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmemTotal) != cudaSuccess ||
-        cudaFuncSetAttribute(tc_frontend_kernel<3, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmemTotal) != cudaSuccess ||
-        cudaFuncSetAttribute(tc_frontend_kernel<3, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmemTotal) != cudaSuccess) {
+    auto cap = [](auto kernel) {
+      return cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmemTotal) != cudaSuccess;
+    };
+    if (cap(tc_frontend_kernel<1, false, false>) || cap(tc_frontend_kernel<1, true, false>) ||
+        cap(tc_frontend_kernel<3, false, false>) || cap(tc_frontend_kernel<3, true, false>) ||
+        cap(tc_frontend_kernel<1, false, true>) || cap(tc_frontend_kernel<1, true, true>) ||
+        cap(tc_frontend_kernel<3, false, true>) || cap(tc_frontend_kernel<3, true, true>)) {
       cudaGetLastError();
       h->tc_ok = false;
     }
@@ -458,6 +461,7 @@ static void fill_params(const b200mel_handle* h, KernelParams& kp) {
   kp.smem_per_warp_floats = h->g_per_warp_floats;
   kp.gate = nullptr;
   kp.gate_value = 0;
+  kp.f32_flag = nullptr;
 }
 
 int b200mel_forward(b200mel_handle* h, const void* pcm, int32_t pcm_dtype, const int64_t* offsets,
@@ -514,29 +518,39 @@ int b200mel_forward(b200mel_handle* h, const void* pcm, int32_t pcm_dtype, const
   const bool tc_fits = t_max > 0 && tc_max_tiles_per_launch(h->sm_count) / ((t_max + (kp.C == 3 ? 126 : 128) - 1) / (kp.C == 3 ? 126 : 128)) >= 1;
   if (kernel == B200MEL_KERNEL_TC && t_max > 0 && !tc_fits)
     return fail(B200MEL_ERR_UNSUPPORTED, "t_max is too large for the tensor-core kernel (use B200MEL_KERNEL_GENERIC)");
-  // float32 PCM, dense rows, kernel = auto: convert to int16 when that is exact (the reference's audio
-  // is int16 / 32768, data.py:98-116) and gate the two kernels on the outcome - no host round trip
+  // float32 PCM, dense rows, kernel = auto: the reference's audio is int16 / 32768 (data.py:98-116), which the
+  // tensor-core kernel can take exactly.  Both kernels are launched and a device flag decides - no host round
+  // trip.  16-byte aligned rows: the tensor-core kernel reads the floats itself (its producers convert and
+  // test them, 369 MB moved instead of 614 MB) and sets the flag; otherwise a conversion kernel writes an
+  // int16 copy first and the tensor-core launch is gated on the flag as well.
   AsyncScratch f32_guard;  // (freed behind both kernels of the pair, and on every error return)
   f32_guard.st = st;
   void*& f32_scratch = f32_guard.p;
   const KernelParams kp_f32 = kp;
   const bool f32_gated = h->tc_ok && kernel == B200MEL_KERNEL_AUTO && t_max > 0 && pcm_dtype == B200MEL_PCM_F32 && !offsets &&
                          tc_aligned && kp.n_masks_f + kp.n_masks_t <= 16 && tc_fits && row_stride > 0;
+  static const bool f32_fused_ok = [] { const char* e = std::getenv("B200MEL_F32_TWO_PASS"); return !(e && std::atoi(e)); }();
+  const bool f32_fused = f32_gated && f32_fused_ok && (reinterpret_cast<uintptr_t>(pcm) & 15) == 0 && (row_stride & 7) == 0 &&
+                         static_cast<int64_t>(batch) * (row_stride >> 3) < 0x7fffffffLL;
   if (f32_gated) {
     const size_t n = static_cast<size_t>(batch) * static_cast<size_t>(row_stride);
-    CU_CHECK(cudaMallocFromPoolAsync(&f32_scratch, 64 + n * sizeof(int16_t), h->pool, st));
+    CU_CHECK(cudaMallocFromPoolAsync(&f32_scratch, 64 + (f32_fused ? 0 : n * sizeof(int16_t)), h->pool, st));
     int32_t* flag = static_cast<int32_t*>(f32_scratch);
-    int16_t* pcm16 = reinterpret_cast<int16_t*>(static_cast<char*>(f32_scratch) + 64);
     CU_CHECK(cudaMemsetAsync(flag, 0, sizeof(int32_t), st));
-    const int64_t per_row_threads = (row_stride + 7) / 8;
-    // (four groups of eight samples per thread and round: 1024 groups per block-round)
-    dim3 cgrid(static_cast<unsigned>(std::min<int64_t>(16, (per_row_threads + 1023) / 1024)), static_cast<unsigned>(batch));
-    pcm_f32_to_i16_kernel<<<cgrid, 256, 0, st>>>(static_cast<const float*>(pcm), lengths, row_stride, pcm16, flag);
-    h->launches.fetch_add(1);
-    kp.pcm = pcm16;
-    kp.pcm_is_f32 = 0;
-    kp.gate = flag;
-    kp.gate_value = 0;
+    if (f32_fused) {
+      kp.f32_flag = flag;   // (pcm_is_f32 stays 1: tc_launch_one picks the float32 instantiation)
+    } else {
+      int16_t* pcm16 = reinterpret_cast<int16_t*>(static_cast<char*>(f32_scratch) + 64);
+      const int64_t per_row_threads = (row_stride + 7) / 8;
+      // (four groups of eight samples per thread and round: 1024 groups per block-round)
+      dim3 cgrid(static_cast<unsigned>(std::min<int64_t>(16, (per_row_threads + 1023) / 1024)), static_cast<unsigned>(batch));
+      pcm_f32_to_i16_kernel<<<cgrid, 256, 0, st>>>(static_cast<const float*>(pcm), lengths, row_stride, pcm16, flag);
+      h->launches.fetch_add(1);
+      kp.pcm = pcm16;
+      kp.pcm_is_f32 = 0;
+      kp.gate = flag;
+      kp.gate_value = 0;
+    }
   }
   // (the tensor-core kernel keeps one mask-table entry per lane: at most 16 masks per utterance)
   if (h->tc_ok && kernel != B200MEL_KERNEL_GENERIC && t_max > 0 && (pcm_dtype == B200MEL_PCM_I16 || f32_gated) && tc_aligned &&
@@ -579,17 +593,20 @@ int b200mel_forward(b200mel_handle* h, const void* pcm, int32_t pcm_dtype, const
     if (tmp_table) cudaFreeAsync(tmp_table, st);
     h->launches.fetch_add(n_launched);
     if (two_stage) {
+      // (float32 input: the second stage runs only when every sample was exact - the flag is final when the
+      //  first stage, which sets it in the fused form, has completed)
+      const int32_t* gate2 = f32_gated ? static_cast<const int32_t*>(f32_scratch) : nullptr;
       if (rc == 0) {
         if (h->d_dct_mma && (reinterpret_cast<uintptr_t>(out) & 31) == 0) {
           const MfccMmaArgs a{lm, out, lengths, t_max, kp.Lw, kp.H, h->d_dct_mma, kp.n_masks_f, kp.n_masks_t, kp.sa_F,
-                              kp.sa_T, kp.sa_p, mask_table, seed, first_utterance_id, status, kp.gate, kp.gate_value,
+                              kp.sa_T, kp.sa_p, mask_table, seed, first_utterance_id, status, gate2, 0,
                               batch, h->sm_count};
           if (mfcc_mma(kp.n_mfcc, kp.C, 1, h->max_smem_optin, a, st) != cudaSuccess) rc = 1;
         } else {
           dim3 grid(static_cast<unsigned>((t_max + kMfccFrames - 1) / kMfccFrames), static_cast<unsigned>(batch));
           mfcc_post_kernel<<<grid, kMfccThreads, mfcc_post_smem_bytes(kp.M, kp.n_mfcc), st>>>(
               lm, out, lengths, t_max, kp.Lw, kp.H, kp.M, kp.n_mfcc, kp.C, kp.dct, kp.n_masks_f, kp.n_masks_t, kp.sa_F,
-              kp.sa_T, kp.sa_p, mask_table, seed, first_utterance_id, status, kp.gate, kp.gate_value);
+              kp.sa_T, kp.sa_p, mask_table, seed, first_utterance_id, status, gate2, 0);
           if (cudaGetLastError() != cudaSuccess) rc = 1;
         }
         h->launches.fetch_add(1);

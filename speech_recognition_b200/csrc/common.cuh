@@ -52,6 +52,9 @@ struct KernelParams {
   // `*gate` (0 = every sample was an exact int16 / 32768) equals its gate_value; null = always run
   const int32_t* gate;
   int32_t gate_value;
+  // float32 PCM read by the tensor-core kernel itself (pcm_is_f32 = 1 there): the kernel ORs 1 into this word
+  // when a sample it used was not an exact int16 / 32768; the generic kernel behind it is gated on the word
+  int32_t* f32_flag;
 };
 
 // ---------------------------------------------------------------------------------------------

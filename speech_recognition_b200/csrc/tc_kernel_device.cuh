@@ -1,6 +1,8 @@
 // tc_kernel_device.cuh - device code of the tensor-core front-end kernel (see tc_kernel.cuh).
 #pragma once
 
+#include "tc_epilogue_math.cuh"
+
 namespace b200mel {
 
 struct TcParams {
@@ -45,6 +47,40 @@ __device__ __forceinline__ void tc_split_pair(uint32_t d, uint32_t& hi_out, uint
   const __half2 lo = __hadd2(e, lq);
   hi_out = *reinterpret_cast<const uint32_t*>(&hi);
   lo_out = *reinterpret_cast<const uint32_t*>(&lo);
+}
+
+// float32 entry (data.py:98-99, 104-105, 116: the reference's audio is int16 / 32768 in float32): eight samples
+// (two 128-bit loads) -> the same four words of packed 16-bit samples the int16 entry loads, plus the
+// exactness test.  m = fma(x, 32768, 1.5 * 2^23) is an integer-valued float whose low 16 bits ARE the
+// two's-complement sample when -32768 <= x * 32768 <= 32767 - its bit pattern then lies in
+// [0x4B3F8000, 0x4B407FFF] (NaN and infinities do not) - and fma(x, 32768, 1.5 * 2^23 - m) is exactly +0.0 iff
+// x * 32768 was that integer.  Nothing is tested per sample: the residuals' bits and the patterns' offsets
+// are OR-ed into two words the thread looks at once, at the end of the kernel.  Three packed f32x2
+// instructions, two integer adds, two LOP3 and one PRMT per pair of samples.
+struct TcF32Check {
+  uint32_t resid = 0;   // OR of the residuals' bit patterns: 0 = every product was an integer
+  uint32_t range = 0;   // OR of (pattern - 0x4B3F8000): < 0x10000 = every sample was inside the int16 range
+  __device__ __forceinline__ bool bad() const { return resid != 0 || range >= 0x10000u; }
+};
+__device__ __forceinline__ uint32_t tc_f32_pair(float x0, float x1, TcF32Check& chk) {
+  const tc_f2 k = tc_pk(32768.0f, 32768.0f), magic = tc_pk(12582912.0f, 12582912.0f), m1 = tc_pk(-1.0f, -1.0f);
+  const tc_f2 x = tc_pk(x0, x1);
+  const tc_f2 m = tc_fma2(x, k, magic);
+  const tc_f2 nback = tc_fma2(m, m1, magic);      // -(m - magic), exact
+  const tc_f2 resid = tc_fma2(x, k, nback);       // x * 32768 - (m - magic), one rounding of the exact value
+  float ma, mb, ra, rb;
+  tc_upk(m, ma, mb);
+  tc_upk(resid, ra, rb);
+  const uint32_t u0 = __float_as_uint(ma), u1 = __float_as_uint(mb);
+  chk.resid |= __float_as_uint(ra) | __float_as_uint(rb);
+  chk.range |= (u0 - 0x4B3F8000u) | (u1 - 0x4B3F8000u);
+  return tc::prmt(u0, u1, 0x5410u);
+}
+__device__ __forceinline__ void tc_f32_block(const uint4 a, const uint4 b, uint32_t* w4, TcF32Check& chk) {
+  w4[0] = tc_f32_pair(__uint_as_float(a.x), __uint_as_float(a.y), chk);
+  w4[1] = tc_f32_pair(__uint_as_float(a.z), __uint_as_float(a.w), chk);
+  w4[2] = tc_f32_pair(__uint_as_float(b.x), __uint_as_float(b.y), chk);
+  w4[3] = tc_f32_pair(__uint_as_float(b.z), __uint_as_float(b.w), chk);
 }
 
 // Swizzled byte offset of element block g (8 elements = 16 bytes) inside a stream: SWIZZLE_64B.

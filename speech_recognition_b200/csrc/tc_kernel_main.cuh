@@ -311,7 +311,10 @@ __device__ __forceinline__ void tc_set_regs() {
   if (N > kTcLaunchRegs) tc::setmaxnreg_inc<N>();
 }
 
-template <int C, bool kMask>
+// kF32: the PCM is float32 (int16 / 32768 as load_audio_file gives it, data.py:98-116), dense rows, 16-byte
+// aligned: the producers convert it back to the 16-bit samples on the fly (tc_f32_block) and OR 1 into
+// p.f32_flag when a sample they used is not exact - the caller then runs the generic kernel behind this one.
+template <int C, bool kMask, bool kF32>
 __global__ void __launch_bounds__(kTcThreads, 1)
     tc_frontend_kernel(const KernelParams p, const TcParams tp, const __grid_constant__ CUtensorMap out_map) {
   extern __shared__ __align__(1024) uint8_t tc_smem_raw[];
@@ -369,8 +372,8 @@ __global__ void __launch_bounds__(kTcThreads, 1)
     if (s0 < 0) s0 = 0;
     if (s1 > p.row_stride) s1 = p.row_stride;
     if (s1 > s0)
-      tc::prefetch_l2(static_cast<const int16_t*>(p.pcm) + static_cast<int64_t>(b0) * p.row_stride + s0,
-                      static_cast<uint32_t>(2 * (s1 - s0)));
+      tc::prefetch_l2(static_cast<const char*>(p.pcm) + (static_cast<int64_t>(b0) * p.row_stride + s0) * (kF32 ? 4 : 2),
+                      static_cast<uint32_t>((kF32 ? 4 : 2) * (s1 - s0)));
   }
   tc::tc_fence_before();
   __syncthreads();
@@ -408,15 +411,44 @@ __global__ void __launch_bounds__(kTcThreads, 1)
     const uint4* pcm16 = reinterpret_cast<const uint4*>(p.pcm);
     uint32_t w[3][20];  // this thread's groups: raw words (two samples each), XOR-ed in place before use
     bool preloaded = false;
+    TcF32Check f32_bad;  // (kF32) did a sample this thread converted fail to be an exact int16 / 32768?
     // raw words of one tile -> w: absolute 8-sample block index, clamped into the utterance
+    // (a group whose five blocks all lie inside the utterance - every group of an interior tile - needs no
+    //  clamping: one base address, immediate offsets; the clamped form is for the utterance's edges)
 #define TC_LOAD_GROUP(I, BLK0, BLO, BHI)                                                               \
-  _Pragma("unroll") for (int q = 0; q < 5; ++q) {                                                      \
-    const int32_t blk = (BLK0) + 5 * (ptid + kTcProducerThreads * (I)) + q;                            \
-    const uint4 v = __ldg(pcm16 + min(max(blk, (BLO)), (BHI)));                                        \
-    w[I][4 * q + 0] = v.x;                                                                             \
-    w[I][4 * q + 1] = v.y;                                                                             \
-    w[I][4 * q + 2] = v.z;                                                                             \
-    w[I][4 * q + 3] = v.w;                                                                             \
+  {                                                                                                    \
+    const int32_t g0 = (BLK0) + 5 * (ptid + kTcProducerThreads * (I));                                 \
+    const bool inside = g0 >= (BLO) && g0 + 4 <= (BHI);                                                \
+    if (kF32) { /* a block of 8 samples = two 128-bit loads of floats; the group's ten loads go out in a row */ \
+      /* (a run of loads = one L2 round trip on the producers' critical path; 18 loads per run were tried:  */ \
+      /*  the 96 registers the kernel is compiled for hold 12, the rest spills - three runs of ten it is)   */ \
+      uint4 t32[10];                                                                                   \
+      if (inside) {                                                                                    \
+        const uint4* src = pcm16 + 2 * static_cast<int64_t>(g0);                                       \
+        _Pragma("unroll") for (int q = 0; q < 10; ++q) t32[q] = tc::ldg_nc_v4(src + q);                \
+      } else {                                                                                         \
+        _Pragma("unroll") for (int q = 0; q < 5; ++q) {                                                \
+          const int64_t blk = min(max(g0 + q, (BLO)), (BHI));                                          \
+          t32[2 * q] = tc::ldg_nc_v4(pcm16 + 2 * blk);                                                 \
+          t32[2 * q + 1] = tc::ldg_nc_v4(pcm16 + 2 * blk + 1);                                         \
+        }                                                                                              \
+      }                                                                                                \
+      _Pragma("unroll") for (int q = 0; q < 5; ++q) tc_f32_block(t32[2 * q], t32[2 * q + 1], &w[I][4 * q], f32_bad); \
+    } else {                                                                                           \
+      uint4 t16[5];                                                                                    \
+      if (inside) {                                                                                    \
+        const uint4* src = pcm16 + g0;                                                                 \
+        _Pragma("unroll") for (int q = 0; q < 5; ++q) t16[q] = __ldg(src + q);                         \
+      } else {                                                                                         \
+        _Pragma("unroll") for (int q = 0; q < 5; ++q) t16[q] = __ldg(pcm16 + min(max(g0 + q, (BLO)), (BHI))); \
+      }                                                                                                \
+      _Pragma("unroll") for (int q = 0; q < 5; ++q) {                                                  \
+        w[I][4 * q + 0] = t16[q].x;                                                                    \
+        w[I][4 * q + 1] = t16[q].y;                                                                    \
+        w[I][4 * q + 2] = t16[q].z;                                                                    \
+        w[I][4 * q + 3] = t16[q].w;                                                                    \
+      }                                                                                                \
+    }                                                                                                  \
   }
 #if !defined(TC_NO_SPEC_FIRST)
     // Dense, 16-byte aligned input: load the CTA's first tile now, while the epilogue warps still build
@@ -427,7 +459,8 @@ __global__ void __launch_bounds__(kTcThreads, 1)
     // by comparing with the list entry below and costs one wasted load.  Measured (r2k, 256 x 15 s):
     // 76.9 -> 76.1 us per launch in the 20-step bench, 72.4 -> 72.0 us in the 100-step one.
     int32_t spec_b = -1, spec_j = -1;
-    if (p.offsets == nullptr && pcm_al && (p.row_stride & 7) == 0 && batch_eff > 0) {
+    // (not with float32 input: samples behind `len` would go through the exactness test)
+    if (!kF32 && p.offsets == nullptr && pcm_al && (p.row_stride & 7) == 0 && batch_eff > 0) {
       const int t0 = static_cast<int>((static_cast<long long>(tp.total_tiles) * blockIdx.x) / gridDim.x);
       spec_b = t0 / tp.tiles_per_utt;
       spec_j = t0 - spec_b * tp.tiles_per_utt;
@@ -464,11 +497,11 @@ __global__ void __launch_bounds__(kTcThreads, 1)
         TC_NEXT_RANGE()
         const int32_t q0 = nb_0 < nb_lo ? nb_lo : nb_0;
         const int32_t q1 = nb_0 + 129 * 20 - 1 < nb_hi ? nb_0 + 129 * 20 - 1 : nb_hi;
-        if (q1 >= q0) tc::prefetch_l2(pcm16 + q0, 16u * (q1 - q0 + 1));
+        if (q1 >= q0) tc::prefetch_l2(pcm16 + (kF32 ? 2 : 1) * static_cast<int64_t>(q0), (kF32 ? 32u : 16u) * (q1 - q0 + 1));
       }
       const uint32_t bb = static_cast<uint32_t>(sList[ti].w);
       const uint32_t par = (n - 1) & 1;
-      if (!(bb & 0x80000000u)) {
+      if (kF32 || !(bb & 0x80000000u)) {   // (float32: the host only takes this kernel for aligned dense rows)
         // Every frame t < n_fr ends at a multiple of 8 samples <= len, so clamping the 8-sample
         // block index into [0, len/8 - 1] never changes a sample a valid frame uses; blocks outside
         // only feed rows that the epilogue zero-fills (t >= n_fr) or drops (t < 0).
@@ -541,6 +574,7 @@ __global__ void __launch_bounds__(kTcThreads, 1)
     }
 #undef TC_NEXT_RANGE
 #undef TC_LOAD_GROUP
+    if (kF32 && f32_bad.bad() && p.f32_flag) atomicOr(p.f32_flag, 1);
   } else if (warp == 0) {
     // ======================= MMA ISSUER (one thread of warp 0) ==================================
     // Warp 0 on purpose: the issuing thread needs an instruction slot every few cycles to keep the
@@ -1048,9 +1082,13 @@ inline int tc_launch_one(const TcPlan& tc, const KernelParams& kp, int sm_count,
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   lc.attrs = attr;
   lc.numAttrs = 1;
+  const bool masks = kp.n_masks_f + kp.n_masks_t > 0, f32 = kp.pcm_is_f32 != 0;
   if (kp.C == 3) {
-    const cudaError_t e = kp.n_masks_f + kp.n_masks_t > 0 ? cudaLaunchKernelEx(&lc, tc_frontend_kernel<3, true>, kp, tp, map)
-                                                          : cudaLaunchKernelEx(&lc, tc_frontend_kernel<3, false>, kp, tp, map);
+    const cudaError_t e =
+        f32 ? (masks ? cudaLaunchKernelEx(&lc, tc_frontend_kernel<3, true, true>, kp, tp, map)
+                     : cudaLaunchKernelEx(&lc, tc_frontend_kernel<3, false, true>, kp, tp, map))
+            : (masks ? cudaLaunchKernelEx(&lc, tc_frontend_kernel<3, true, false>, kp, tp, map)
+                     : cudaLaunchKernelEx(&lc, tc_frontend_kernel<3, false, false>, kp, tp, map));
     if (e != cudaSuccess) return 1;
   } else {
     // output viewed as a 3-D tensor [B][t_max][80] f32; box = [1][32][84]
@@ -1063,8 +1101,11 @@ inline int tc_launch_one(const TcPlan& tc, const KernelParams& kp, int sm_count,
     if (enc(&map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, kp.out, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
             CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
       return 2;
-    const cudaError_t e = kp.n_masks_f + kp.n_masks_t > 0 ? cudaLaunchKernelEx(&lc, tc_frontend_kernel<1, true>, kp, tp, map)
-                                                          : cudaLaunchKernelEx(&lc, tc_frontend_kernel<1, false>, kp, tp, map);
+    const cudaError_t e =
+        f32 ? (masks ? cudaLaunchKernelEx(&lc, tc_frontend_kernel<1, true, true>, kp, tp, map)
+                     : cudaLaunchKernelEx(&lc, tc_frontend_kernel<1, false, true>, kp, tp, map))
+            : (masks ? cudaLaunchKernelEx(&lc, tc_frontend_kernel<1, true, false>, kp, tp, map)
+                     : cudaLaunchKernelEx(&lc, tc_frontend_kernel<1, false, false>, kp, tp, map));
     if (e != cudaSuccess) return 1;
   }
   return cudaGetLastError() == cudaSuccess ? 0 : 1;
