@@ -266,6 +266,10 @@ __global__ void __launch_bounds__(kMfccThreads)
 // per quad, every sector used once - and uses the four values as fragment columns 2 tq, 2 tq + 1,
 // 2 tq + 8, 2 tq + 9 of k-step j.  The host stores the image in the same order, one 16-byte entry
 // (b0 hi, b1 hi, b0 lo, b1 lo) per (k-step, tq, coefficient): one 128-bit load per fragment.
+//   The DCT-II matrix is mirror-symmetric, d[M - 1 - m][c] = (-1)^c d[m][c], so the products are halved:
+// even coefficients come from s[m] = x[m] + x[M - 1 - m], odd ones from a[m] = x[m] - x[M - 1 - m]
+// (m < 40), two [rows x 40] x [40 x n_mfcc / 2] products (K padded to 48 = 3 k-steps, N to whole n-tiles).
+// A lane's accumulators of one n-tile pair are four consecutive coefficients.
 //   Copy-out items are (row, 8 coefficients): 32 bytes (C = 1) or 96 bytes (C = 3) of whole sectors,
 // written with 256-bit stores: `out` must be 32-byte aligned.
 //   History (256 x 15 s, MFCC-40 + delta, second stage alone): TF32 m16n8k8, rows staged in shared
@@ -287,11 +291,17 @@ __host__ __device__ constexpr int mfcc_mma_image_pitch(int n_mfcc) {
   while ((p & 7) != 2) ++p;
   return p;
 }
-// mel bin multiplied by fragment column s (0..15) of k-step j for lane-quad column tq = (s & 7) >> 1
+// folded mel index m (< 40; >= 40 = padding) multiplied by fragment column s (0..15) of k-step j (0..2), for
+// lane-quad column tq = (s & 7) >> 1
 __host__ __device__ constexpr int mfcc_mma_image_k(int j, int s) {
   return 16 * j + 4 * ((s & 7) >> 1) + 2 * (s >> 3) + (s & 1);
 }
-inline size_t mfcc_mma_image_words(int n_mfcc) { return static_cast<size_t>(kMfccMmaM / 16) * 4 * mfcc_mma_image_pitch(n_mfcc) * 4; }
+constexpr int kMfccMmaKSteps = 3;   // 40 folded mel bins in k-steps of 16
+__host__ __device__ constexpr int mfcc_mma_ntiles(int n_mfcc) { return (n_mfcc / 2 + 7) / 8; }   // n-tiles per parity
+// image: [parity][k-step][tq][PN] entries of 16 bytes, PN = pitch of the parity's 8 * ntiles columns
+inline size_t mfcc_mma_image_words(int n_mfcc) {
+  return static_cast<size_t>(2) * kMfccMmaKSteps * 4 * mfcc_mma_image_pitch(8 * mfcc_mma_ntiles(n_mfcc)) * 4;
+}
 inline size_t mfcc_post_mma_smem_bytes(int n_mfcc) {
   return sizeof(float) * (static_cast<size_t>(kMfccMmaRows) * mfcc_mma_pitch(n_mfcc) + mfcc_mma_image_words(n_mfcc));
 }
@@ -323,11 +333,12 @@ __global__ void __launch_bounds__(kMfccMmaThreads, 3)
                          const int32_t* __restrict__ gate, int gate_value) {
   extern __shared__ __align__(16) float mfcc_smem[];
   if (gate && (*gate != 0) != (gate_value != 0)) return;
-  constexpr int M = kMfccMmaM, n_mfcc = 8 * NT, P = mfcc_mma_pitch(n_mfcc), PN = mfcc_mma_image_pitch(n_mfcc);
+  constexpr int M = kMfccMmaM, n_mfcc = 8 * NT, P = mfcc_mma_pitch(n_mfcc);
+  constexpr int NP = mfcc_mma_ntiles(n_mfcc), PN = mfcc_mma_image_pitch(8 * NP);   // n-tiles per parity, image pitch
   constexpr int halo = C == 3 ? 2 : 0, new_rows = kMfccMmaRows - halo;
-  constexpr int kImageVec = (M / 16) * 4 * PN;                                // 16-byte entries of the image
+  constexpr int kImageVec = 2 * kMfccMmaKSteps * 4 * PN;                      // 16-byte entries of the image
   float* sc = mfcc_smem;                                                      // [128][P] coefficient rows of the tile
-  const uint4* sd = reinterpret_cast<const uint4*>(mfcc_smem + kMfccMmaRows * P);  // [5][4][PN] (b0 hi, b1 hi, b0 lo, b1 lo)
+  const uint4* sd = reinterpret_cast<const uint4*>(mfcc_smem + kMfccMmaRows * P);  // [2][3][4][PN] (b0 hi, b1 hi, b0 lo, b1 lo)
   __shared__ int32_t s_table[2 * kMaxMasks];
   // Work: the batch's tiles in one flat index (utterance-major), cut into gridDim.x contiguous runs - one
   // resident wave of blocks, no tail wave; `reverse` walks the index from the end.
@@ -376,17 +387,21 @@ __global__ void __launch_bounds__(kMfccMmaThreads, 3)
       for (int i = threadIdx.x; i < n8; i += kMfccMmaThreads) mfcc_st_v8(o + 8 * i, z);
       continue;
     }
-    // this lane's rows: 16 warp + g and + 8; raw log-mel values x[16 j + 4 tq .. + 3], j = 0..4
-    float4 xa[5], xb[5];
+    // this lane's rows: 16 warp + g and + 8.  Raw log-mel values of k-step j: x[16 j + 4 tq .. + 3] and their
+    // mirror images x[79 - m] = the float4 at 76 - 16 j - 4 tq, reversed; k-step 2 only holds m = 32..39 (tq < 2)
+    float4 xa[3], ya[3], xb[3], yb[3];
     {
       const int64_t ta = t0 - halo + 16 * warp + g, tb = ta + 8;
       const bool la = ta >= 0 && ta < n_fr, lb = tb >= 0 && tb < n_fr;
-      const float4* pa = reinterpret_cast<const float4*>(lmb + ta * M) + tq;
+      const float4* pa = reinterpret_cast<const float4*>(lmb + ta * M);
       const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
-      for (int j = 0; j < 5; ++j) {
-        xa[j] = la ? __ldg(pa + 4 * j) : z;
-        xb[j] = lb ? __ldg(pa + 2 * M + 4 * j) : z;
+      for (int j = 0; j < 3; ++j) {
+        const bool kj = j < 2 || tq < 2;
+        xa[j] = la && kj ? __ldg(pa + 4 * j + tq) : z;
+        ya[j] = la && kj ? __ldg(pa + 19 - 4 * j - tq) : z;
+        xb[j] = lb && kj ? __ldg(pa + 2 * M + 4 * j + tq) : z;
+        yb[j] = lb && kj ? __ldg(pa + 2 * M + 19 - 4 * j - tq) : z;
       }
     }
     if (w + 1 < w1) {
@@ -399,41 +414,55 @@ __global__ void __launch_bounds__(kMfccMmaThreads, 3)
       const int64_t n_lines = ((r1 - r0) * M * 4 + 127) >> 7;
       for (int64_t i = threadIdx.x; i < n_lines; i += kMfccMmaThreads) asm volatile("prefetch.global.L2 [%0];" ::"l"(base + 32 * i));
     }
-    float acc[NT][4];
+    float acc[2][NP][4];   // [parity][n-tile][fragment]
 #pragma unroll
-    for (int nt = 0; nt < NT; ++nt)
+    for (int par = 0; par < 2; ++par)
 #pragma unroll
-      for (int i = 0; i < 4; ++i) acc[nt][i] = 0.0f;
+      for (int nt = 0; nt < NP; ++nt)
 #pragma unroll
-    for (int j = 0; j < M / 16; ++j) {
-      uint32_t ah[4], al[4];   // a0 = row g cols (2tq, 2tq+1), a1 = row g+8 same, a2 = row g cols (2tq+8, +9), a3 = row g+8 same
-      mfcc_split_f16(xa[j].x, xa[j].y, ah[0], al[0]);
-      mfcc_split_f16(xb[j].x, xb[j].y, ah[1], al[1]);
-      mfcc_split_f16(xa[j].z, xa[j].w, ah[2], al[2]);
-      mfcc_split_f16(xb[j].z, xb[j].w, ah[3], al[3]);
-      const uint4* bp = sd + (4 * j + tq) * PN + g;
+        for (int i = 0; i < 4; ++i) acc[par][nt][i] = 0.0f;
 #pragma unroll
-      for (int nt = 0; nt < NT; ++nt) {
-        const uint4 bb = bp[8 * nt];   // (b0 hi, b1 hi, b0 lo, b1 lo)
-        mfcc_mma_f16(acc[nt], al, bb.x, bb.y);
-        mfcc_mma_f16(acc[nt], ah, bb.z, bb.w);
-        mfcc_mma_f16(acc[nt], ah, bb.x, bb.y);
+    for (int j = 0; j < kMfccMmaKSteps; ++j) {
+#pragma unroll
+      for (int par = 0; par < 2; ++par) {
+        // folded operand: s = x + mirror (even coefficients), a = x - mirror (odd ones)
+        const float sg = par ? -1.0f : 1.0f;
+        const float fa[4] = {fmaf(sg, ya[j].w, xa[j].x), fmaf(sg, ya[j].z, xa[j].y), fmaf(sg, ya[j].y, xa[j].z), fmaf(sg, ya[j].x, xa[j].w)};
+        const float fb[4] = {fmaf(sg, yb[j].w, xb[j].x), fmaf(sg, yb[j].z, xb[j].y), fmaf(sg, yb[j].y, xb[j].z), fmaf(sg, yb[j].x, xb[j].w)};
+        uint32_t ah[4], al[4];   // a0 = row g cols (2tq, 2tq+1), a1 = row g+8 same, a2 = row g cols (2tq+8, +9), a3 = row g+8 same
+        mfcc_split_f16(fa[0], fa[1], ah[0], al[0]);
+        mfcc_split_f16(fb[0], fb[1], ah[1], al[1]);
+        mfcc_split_f16(fa[2], fa[3], ah[2], al[2]);
+        mfcc_split_f16(fb[2], fb[3], ah[3], al[3]);
+        const uint4* bp = sd + ((par * kMfccMmaKSteps + j) * 4 + tq) * PN + g;
+#pragma unroll
+        for (int nt = 0; nt < NP; ++nt) {
+          const uint4 bb = bp[8 * nt];   // (b0 hi, b1 hi, b0 lo, b1 lo)
+          mfcc_mma_f16(acc[par][nt], al, bb.x, bb.y);
+          mfcc_mma_f16(acc[par][nt], ah, bb.z, bb.w);
+          mfcc_mma_f16(acc[par][nt], ah, bb.x, bb.y);
+        }
       }
     }
+    // fragment column n = 8 nt + 2 tq (+1) of parity par is coefficient 2 n + par: a lane's values of one n-tile
+    // are the four consecutive coefficients 16 nt + 4 tq .. + 3
 #pragma unroll
     for (int half = 0; half < 2; ++half) {
       const int r = 16 * warp + g + 8 * half;
       const int64_t t = t0 - halo + r;
       const bool live = t >= 0 && t < n_fr;
 #pragma unroll
-      for (int nt = 0; nt < NT; ++nt) {
-        const int c = 8 * nt + 2 * tq;
-        float v0 = live ? acc[nt][2 * half] : 0.0f, v1 = live ? acc[nt][2 * half + 1] : 0.0f;
-        if (n_masks > 0 && live) {
-          v0 *= mask_value(s_table, n_masks_f, n_masks_t, static_cast<int>(t), c);
-          v1 *= mask_value(s_table, n_masks_f, n_masks_t, static_cast<int>(t), c + 1);
+      for (int nt = 0; nt < NP; ++nt) {
+        const int c = 16 * nt + 4 * tq;
+        if (c < n_mfcc) {
+          float v[4] = {acc[0][nt][2 * half], acc[1][nt][2 * half], acc[0][nt][2 * half + 1], acc[1][nt][2 * half + 1]};
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            v[i] = live ? v[i] : 0.0f;
+            if (n_masks > 0 && live) v[i] *= mask_value(s_table, n_masks_f, n_masks_t, static_cast<int>(t), c + i);
+          }
+          *reinterpret_cast<float4*>(sc + r * P + c) = make_float4(v[0], v[1], v[2], v[3]);
         }
-        *reinterpret_cast<float2*>(sc + r * P + c) = make_float2(v0, v1);
       }
     }
     __syncthreads();

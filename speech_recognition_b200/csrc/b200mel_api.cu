@@ -313,30 +313,32 @@ int b200mel_create(const b200mel_config* config, int device, b200mel_handle** ou
     }
   }
   if (h->tc_ok && p.cfg.audio_feature_type == B200MEL_FEATURE_MFCC && mfcc_mma_shape_ok(p.cfg.num_mel_bins, p.n_mfcc_eff)) {
-    // the DCT matrix split into f16 (hi, lo) parts, in the shared-memory layout of mfcc_post_mma_kernel:
-    // entry (k-step j, tq, coefficient n) = (b0 hi, b1 hi, b0 lo, b1 lo), b0 = fragment columns (2 tq, 2 tq + 1),
-    // b1 = (2 tq + 8, 2 tq + 9), each a packed pair of halves (low half = the even column)
-    const int M = p.cfg.num_mel_bins, nm = p.n_mfcc_eff, PN = mfcc_mma_image_pitch(nm);
+    // the DCT matrix split into f16 (hi, lo) parts, in the shared-memory layout of mfcc_post_mma_kernel: rows
+    // folded by the mirror symmetry (m < 40; parity 0 = even coefficients, 1 = odd), entry (parity, k-step j,
+    // tq, n) = (b0 hi, b1 hi, b0 lo, b1 lo) for coefficient 2 n + parity, b0 = fragment columns (2 tq,
+    // 2 tq + 1), b1 = (2 tq + 8, 2 tq + 9), each a packed pair of halves (low half = the even column)
+    const int M = p.cfg.num_mel_bins, nm = p.n_mfcc_eff, PN = mfcc_mma_image_pitch(8 * mfcc_mma_ntiles(nm));
     std::vector<uint32_t> img(mfcc_mma_image_words(nm), 0u);
     auto split = [&](int k, int c, uint16_t& hi, uint16_t& lo) {
-      const float d = p.dct[static_cast<size_t>(k) * nm + c];
+      const float d = (k < M / 2 && c < nm) ? p.dct[static_cast<size_t>(k) * nm + c] : 0.0f;
       const __half h = __float2half_rn(d);
       const __half l = __float2half_rn(d - __half2float(h));
       std::memcpy(&hi, &h, 2);
       std::memcpy(&lo, &l, 2);
     };
-    for (int j = 0; j < M / 16; ++j)
-      for (int tq = 0; tq < 4; ++tq)
-        for (int c = 0; c < nm; ++c) {
-          uint32_t* e = &img[(static_cast<size_t>(4 * j + tq) * PN + c) * 4];
-          for (int part = 0; part < 2; ++part) {   // b0, b1
-            uint16_t h0, l0, h1, l1;
-            split(mfcc_mma_image_k(j, 2 * tq + 8 * part), c, h0, l0);
-            split(mfcc_mma_image_k(j, 2 * tq + 8 * part + 1), c, h1, l1);
-            e[part] = static_cast<uint32_t>(h0) | (static_cast<uint32_t>(h1) << 16);
-            e[2 + part] = static_cast<uint32_t>(l0) | (static_cast<uint32_t>(l1) << 16);
+    for (int par = 0; par < 2; ++par)
+      for (int j = 0; j < kMfccMmaKSteps; ++j)
+        for (int tq = 0; tq < 4; ++tq)
+          for (int n = 0; n < 8 * mfcc_mma_ntiles(nm); ++n) {
+            uint32_t* e = &img[(static_cast<size_t>((par * kMfccMmaKSteps + j) * 4 + tq) * PN + n) * 4];
+            for (int part = 0; part < 2; ++part) {   // b0, b1
+              uint16_t h0, l0, h1, l1;
+              split(mfcc_mma_image_k(j, 2 * tq + 8 * part), 2 * n + par, h0, l0);
+              split(mfcc_mma_image_k(j, 2 * tq + 8 * part + 1), 2 * n + par, h1, l1);
+              e[part] = static_cast<uint32_t>(h0) | (static_cast<uint32_t>(h1) << 16);
+              e[2 + part] = static_cast<uint32_t>(l0) | (static_cast<uint32_t>(l1) << 16);
+            }
           }
-        }
     MfccMmaArgs none{};
     if (upload(img, &h->d_dct_mma) != cudaSuccess ||
         mfcc_mma(nm, 1, 0, h->max_smem_optin, none, nullptr) != cudaSuccess ||
