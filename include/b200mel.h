@@ -196,6 +196,17 @@ int b200mel_specaug_apply(const float* in, float* out, int32_t batch, int64_t t_
                           int32_t channels, const int32_t* table, int32_t m_F, int32_t m_T,
                           void* stream);
 
+/* SpecAugment time warp (data.py:275-280: tfa.image.sparse_image_warp with one control point (src_t, v/2) ->
+ * (dst_t, v/2) and num_boundary_points = 3) on [B, t_max, v, channels] features, per utterance over its own
+ * n_frames[b] rows (clipped to t_max); rows behind them are written as +0.0.  src_t / dst_t are drawn like the
+ * reference draws them (uniform(W, T - W) and src + uniform(-W, W); Philox stream 1 of (seed, utterance id)), or
+ * taken from warp_table (device int32 [B, 2], e.g. recorded TF draws).  An utterance the reference's draw would
+ * raise on (T - W <= W) is copied unchanged and bit 0 of *status is set.  Not in place.  tensorflow-addons is an
+ * un-vendored dependency of the reference: parity unpinned (oracle/time_warp_oracle.py). */
+int b200mel_time_warp(const float* in, float* out, const int32_t* n_frames, int32_t batch, int64_t t_max,
+                      int32_t v, int32_t channels, int32_t W, const int32_t* warp_table, uint64_t seed,
+                      uint64_t first_utterance_id, int32_t* status, void* stream);
+
 /* delta_accelerate (data.py:310-328): [B, t_max, v, 1] -> [B, t_max, v, 3]. n_frames (device
  * int32[B] or NULL) keeps the padding rows at zero. */
 int b200mel_delta(const float* in, float* out, const int32_t* n_frames, int32_t batch,

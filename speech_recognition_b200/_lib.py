@@ -69,6 +69,7 @@ SIGNATURES = {
                                         _vp, _vp, _vp]),
     "b200mel_specaug_apply": (_c.c_int, [_vp, _vp, _i32, _i64, _i32, _i32, _vp, _i32, _i32, _vp]),
     "b200mel_delta": (_c.c_int, [_vp, _vp, _vp, _i32, _i64, _i32, _vp]),
+    "b200mel_time_warp": (_c.c_int, [_vp, _vp, _vp, _i32, _i64, _i32, _i32, _i32, _vp, _u64, _u64, _vp, _vp]),
     "b200mel_wav_parse": (_c.c_int, [_vp, _i64, _c.POINTER(_i32), _c.POINTER(_i32), _c.POINTER(_i32),
                                      _c.POINTER(_i32), _c.POINTER(_i64), _c.POINTER(_i64)]),
     "b200mel_ingest_pcm16": (_c.c_int, [_vp, _vp, _vp, _vp, _i32, _vp, _i32, _vp, _i64, _vp, _vp]),

@@ -500,6 +500,154 @@ __global__ void __launch_bounds__(kMfccMmaThreads, 3)
 }
 
 // ---------------------------------------------------------------------------------------------
+// SpecAugment time warp (data.py:275-280):
+//   tfa.image.sparse_image_warp(audio [T, v, C], src = (src_t, v / 2), dst = (dst_t, v / 2), num_boundary_points = 3)
+// = a polyharmonic spline (order 2, phi(r) = 0.5 r log max(r, 1e-10) of the squared distance r) through 13
+// control flows - the drawn point's (dst_t - src_t, 0) and zero at the 12 boundary points of a 4 x 4 grid over
+// the [T, v] image - evaluated at every pixel, then dense_image_warp: bilinear sampling at (y, x) - flow.  The
+// frequency component of every control flow is zero, so the x-flow vanishes identically and the warp moves
+// frames along time only.  tensorflow-addons is not vendored by the reference: parity unpinned
+// (oracle/time_warp_oracle.py restates the published algorithm).
+//   time_warp_solve_kernel: one thread per utterance - the two draws (Philox stream 1: the mask draws,
+// stream 0, are the same with or without the warp), the 16 x 16 system [[A, B], [B^T, 0]] in float64
+// (its condition number is ~1e15 in these units; TF solves it in float32), Gaussian elimination with partial
+// pivoting; result: 13 weights + 3 linear terms of the time flow as float32, and dst_t.
+//   time_warp_apply_kernel: one thread per (frame, bin): 13 phi terms, one linear interpolation along time per
+// channel (written as TF's bilinear formula, so the last bin's alpha = 1 rounds like TF's).
+// ---------------------------------------------------------------------------------------------
+constexpr int kWarpPoints = 13, kWarpSystem = 16, kWarpCoefFloats = 20;   // w[13], v[3], dst_t, valid, T, pad
+// control point i of an utterance with T frames and v bins: (y, x); i = 0 is the drawn point
+__host__ __device__ inline void warp_control_point(int i, int T, int v, float dst_t, double& y, double& x) {
+  if (i == 0) {
+    y = dst_t;
+    x = static_cast<double>(v / 2);
+    return;
+  }
+  // boundary points of the 4 x 4 grid in row-major order: row 0 (4), rows 1-2 (first / last column), row 3 (4)
+  int gi, gj;
+  const int k = i - 1;
+  if (k < 4) { gi = 0; gj = k; }
+  else if (k < 8) { gi = 1 + (k - 4) / 2; gj = ((k - 4) & 1) ? 3 : 0; }
+  else { gi = 3; gj = k - 8; }
+  y = gi == 3 ? static_cast<double>(T - 1) : static_cast<double>(gi) * static_cast<double>(T - 1) / 3.0;
+  x = gj == 3 ? static_cast<double>(v - 1) : static_cast<double>(gj) * static_cast<double>(v - 1) / 3.0;
+}
+__host__ __device__ inline uint32_t warp_raw_draw(uint64_t seed, uint64_t utt, uint32_t idx) {
+  return philox4x32_10_first(idx, 1u, static_cast<uint32_t>(utt), static_cast<uint32_t>(utt >> 32),
+                             static_cast<uint32_t>(seed), static_cast<uint32_t>(seed >> 32));
+}
+__global__ void time_warp_solve_kernel(const int32_t* __restrict__ n_frames, int batch, int64_t t_max, int v, int W,
+                                       const int32_t* __restrict__ warp_table, uint64_t seed, uint64_t first_utt,
+                                       float* __restrict__ coef, int32_t* status) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= batch) return;
+  float* out = coef + static_cast<size_t>(b) * kWarpCoefFloats;
+  const int64_t nf = n_frames[b];
+  const int T = static_cast<int>(nf < t_max ? nf : t_max);
+  for (int i = 0; i < kWarpCoefFloats; ++i) out[i] = 0.0f;
+  out[18] = static_cast<float>(T);
+  int src_t, dst_t;
+  if (warp_table) {
+    src_t = warp_table[2 * b];
+    dst_t = warp_table[2 * b + 1];
+    if (T < 2 || v < 2) { if (status) atomicOr(status, 1); return; }
+  } else {
+    // tf.random.uniform((), W, num_time - W) raises when maxval <= minval: flagged, the utterance is copied
+    if (T < 2 || v < 2 || T - W <= W || W <= 0) { if (status) atomicOr(status, 1); return; }
+    src_t = W + static_cast<int>(warp_raw_draw(seed, first_utt + static_cast<uint64_t>(b), 0) % static_cast<uint32_t>(T - 2 * W));
+    dst_t = src_t + (-W + static_cast<int>(warp_raw_draw(seed, first_utt + static_cast<uint64_t>(b), 1) % static_cast<uint32_t>(2 * W)));
+  }
+  double m[kWarpSystem][kWarpSystem + 1];
+  double cy[kWarpPoints], cx[kWarpPoints];
+  for (int i = 0; i < kWarpPoints; ++i) warp_control_point(i, T, v, static_cast<float>(dst_t), cy[i], cx[i]);
+  for (int i = 0; i < kWarpSystem; ++i)
+    for (int j = 0; j <= kWarpSystem; ++j) m[i][j] = 0.0;
+  for (int i = 0; i < kWarpPoints; ++i) {
+    for (int j = 0; j < kWarpPoints; ++j) {
+      const double dy = cy[i] - cy[j], dx = cx[i] - cx[j], r = dy * dy + dx * dx;
+      m[i][j] = 0.5 * r * log(r > 1e-10 ? r : 1e-10);
+    }
+    m[i][13] = cy[i]; m[i][14] = cx[i]; m[i][15] = 1.0;
+    m[13][i] = cy[i]; m[14][i] = cx[i]; m[15][i] = 1.0;
+  }
+  m[0][kWarpSystem] = static_cast<double>(dst_t - src_t);   // the only non-zero control flow (time component)
+  for (int col = 0; col < kWarpSystem; ++col) {
+    int piv = col;
+    double best = fabs(m[col][col]);
+    for (int r = col + 1; r < kWarpSystem; ++r)
+      if (fabs(m[r][col]) > best) { best = fabs(m[r][col]); piv = r; }
+    if (best == 0.0) { if (status) atomicOr(status, 2); return; }
+    if (piv != col)
+      for (int j = col; j <= kWarpSystem; ++j) { const double t = m[col][j]; m[col][j] = m[piv][j]; m[piv][j] = t; }
+    const double inv = 1.0 / m[col][col];
+    for (int r = col + 1; r < kWarpSystem; ++r) {
+      const double f = m[r][col] * inv;
+      if (f != 0.0)
+        for (int j = col; j <= kWarpSystem; ++j) m[r][j] -= f * m[col][j];
+    }
+  }
+  double sol[kWarpSystem];
+  for (int r = kWarpSystem - 1; r >= 0; --r) {
+    double acc = m[r][kWarpSystem];
+    for (int j = r + 1; j < kWarpSystem; ++j) acc -= m[r][j] * sol[j];
+    sol[r] = acc / m[r][r];
+  }
+  for (int i = 0; i < kWarpSystem; ++i) out[i] = static_cast<float>(sol[i]);
+  out[16] = static_cast<float>(dst_t);
+  out[17] = 1.0f;   // valid
+}
+__global__ void __launch_bounds__(256)
+    time_warp_apply_kernel(const float* __restrict__ in, float* __restrict__ out, const float* __restrict__ coef,
+                           int64_t t_max, int v, int C) {
+  __shared__ float s_c[kWarpCoefFloats];
+  __shared__ float s_py[kWarpPoints], s_px[kWarpPoints];
+  const int b = blockIdx.y;
+  if (threadIdx.x < kWarpCoefFloats) s_c[threadIdx.x] = coef[static_cast<size_t>(b) * kWarpCoefFloats + threadIdx.x];
+  __syncthreads();
+  const int T = static_cast<int>(s_c[18]);
+  const bool valid = s_c[17] != 0.0f;
+  if (threadIdx.x < kWarpPoints) {
+    double y, x;
+    warp_control_point(threadIdx.x, T, v, s_c[16], y, x);
+    s_py[threadIdx.x] = static_cast<float>(y);
+    s_px[threadIdx.x] = static_cast<float>(x);
+  }
+  __syncthreads();
+  const int64_t pix = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (pix >= t_max * v) return;
+  const int t = static_cast<int>(pix / v), f = static_cast<int>(pix - static_cast<int64_t>(t) * v);
+  const float* inb = in + static_cast<int64_t>(b) * t_max * v * C;
+  float* o = out + (static_cast<int64_t>(b) * t_max * v + pix) * C;
+  if (t >= T) {   // padding stays +0.0
+    for (int c = 0; c < C; ++c) o[c] = 0.0f;
+    return;
+  }
+  if (!valid) {
+    for (int c = 0; c < C; ++c) o[c] = inb[pix * C + c];
+    return;
+  }
+  const float fy = static_cast<float>(t), fx = static_cast<float>(f);
+  float flow = fmaf(s_c[13], fy, fmaf(s_c[14], fx, s_c[15]));
+#pragma unroll
+  for (int i = 0; i < kWarpPoints; ++i) {
+    const float dy = fy - s_py[i], dx = fx - s_px[i], r = fmaf(dy, dy, dx * dx);
+    flow = fmaf(s_c[i], 0.5f * r * __logf(fmaxf(r, 1e-10f)), flow);
+  }
+  const float qy = fy - flow;
+  const float y0 = fminf(fmaxf(floorf(qy), 0.0f), static_cast<float>(T - 2));
+  const float ay = fminf(fmaxf(qy - y0, 0.0f), 1.0f);
+  const int iy = static_cast<int>(y0), ix = f < v - 2 ? f : v - 2;
+  const float ax = static_cast<float>(f - ix);
+  const float* top = inb + (static_cast<int64_t>(iy) * v + ix) * C;
+  const float* bot = top + static_cast<int64_t>(v) * C;
+  for (int c = 0; c < C; ++c) {
+    const float tl = top[c], tr = top[C + c], bl = bot[c], br = bot[C + c];
+    const float it = fmaf(ax, tr - tl, tl), ib = fmaf(ax, br - bl, bl);
+    o[c] = fmaf(ay, ib - it, it);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
 // float32 PCM entry of the tensor-core path.  The reference's audio is int16 / 32768 in float32
 // (load_audio_file, data.py:98-99, 104-105, 116): such samples convert back to int16 exactly and the
 // tensor-core kernel (whose operand split is exact for 16-bit samples) can take them.  Dense [B,

@@ -996,6 +996,34 @@ int b200mel_delta(const float* in, float* out, const int32_t* n_frames, int32_t 
   return B200MEL_OK;
 }
 
+int b200mel_time_warp(const float* in, float* out, const int32_t* n_frames, int32_t batch, int64_t t_max, int32_t v,
+                      int32_t channels, int32_t W, const int32_t* warp_table, uint64_t seed, uint64_t first_utterance_id,
+                      int32_t* status, void* stream) {
+  if (batch < 0 || t_max < 0 || v < 0 || channels < 0) return fail(B200MEL_ERR_INVALID_ARGUMENT, "negative size");
+  if (batch > 65535) return fail(B200MEL_ERR_UNSUPPORTED, "batch > 65535: split the call");
+  if (W <= 0 && !warp_table) return fail(B200MEL_ERR_INVALID_ARGUMENT, "time warp needs W > 0 or a warp_table");
+  if (t_max > (int64_t{1} << 24)) return fail(B200MEL_ERR_UNSUPPORTED, "t_max too large for the float32 pixel grid");
+  const int64_t pixels = t_max * v;
+  if (batch == 0 || pixels == 0 || channels == 0) return B200MEL_OK;
+  if (!in || !out || !n_frames) return fail(B200MEL_ERR_INVALID_ARGUMENT, "null buffer");
+  if (in == out) return fail(B200MEL_ERR_INVALID_ARGUMENT, "the time warp cannot run in place");
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  AsyncScratch coef;   // [batch][kWarpCoefFloats], stream-ordered
+  coef.st = st;
+  CU_CHECK(cudaMallocAsync(&coef.p, static_cast<size_t>(batch) * kWarpCoefFloats * sizeof(float), st));
+  time_warp_solve_kernel<<<(batch + 63) / 64, 64, 0, st>>>(n_frames, batch, t_max, v, W, warp_table, seed, first_utterance_id,
+                                                          static_cast<float*>(coef.p), status);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return cuda_fail(e, "time_warp_solve_kernel launch");
+  const int64_t blocks = (pixels + 255) / 256;
+  if (blocks > 0x7fffffffLL) return fail(B200MEL_ERR_UNSUPPORTED, "t_max * v too large");
+  time_warp_apply_kernel<<<dim3(static_cast<unsigned>(blocks), static_cast<unsigned>(batch)), 256, 0, st>>>(
+      in, out, static_cast<const float*>(coef.p), t_max, v, channels);
+  e = cudaGetLastError();
+  if (e != cudaSuccess) return cuda_fail(e, "time_warp_apply_kernel launch");
+  return B200MEL_OK;
+}
+
 int b200mel_wav_parse(const void* file_bytes, int64_t n_bytes, int32_t* format, int32_t* channels,
                       int32_t* sample_rate, int32_t* bits_per_sample, int64_t* data_offset, int64_t* data_bytes) {
   if (!file_bytes || n_bytes < 0) return fail(B200MEL_ERR_INVALID_ARGUMENT, "null or negative-size file image");

@@ -151,20 +151,25 @@ def spec_augment(
     p: Optional[float] = None,
     m_T: Optional[int] = None,
 ):
-    """data.py:244-307 (frequency and time masking).  The wrapper takes a feature
-    [TimeStep, v, Channel] and returns the masked copy.  Draw order and integer mapping follow the
+    """data.py:244-307 (time warping, frequency and time masking).  The wrapper takes a feature
+    [TimeStep, v, Channel] and returns the augmented copy.  Draw order and integer mapping follow the
     reference ((f, f_0) x m_F then (t, t_0) x m_T; lo + u32 % range); the stream is
-    Philox4x32-10 keyed by (set_random_seed seed, running utterance index).  A draw that TF would
-    reject (``maxval <= minval``) raises ValueError.  Time warping (``W``, data.py:275-280) is
-    outside the hot-path scope and raises NotImplementedError."""
-    if W:
-        raise NotImplementedError("SpecAugment time warping (W) is not supported; every shipped config sets W: null")
+    Philox4x32-10 keyed by (set_random_seed seed, running utterance index); the two draws of the time
+    warp (``W``, data.py:275-280: tfa.image.sparse_image_warp, restated in oracle/time_warp_oracle.py) come
+    from a second stream of the same key, so the masks are the same with or without the warp.  A draw that
+    TF would reject (``maxval <= minval``) raises ValueError."""
 
     def _wrapper(audio, text=None, utterance_id: Optional[int] = None, seed: Optional[int] = None):
         feat = _to_device_feature(audio)
         g_seed, g_utt = _next_utterance()
         seed_ = g_seed if seed is None else seed
         utt = g_utt if utterance_id is None else utterance_id
+        if W:
+            warped, st_w = _fe.time_warp(feat[None], [feat.shape[0]], int(W), seed_, utt)
+            if int(st_w.item()) != 0:
+                raise ValueError("spec_augment: time warp draw had maxval <= minval (num_time - W <= W; "
+                                 "TF raises InvalidArgumentError here)")
+            feat = warped[0]
         table, nf, nt, status = _fe.specaug_draw([feat.shape[0]], v, F, m_F, T, p, m_T, seed_, utt, feat.device)
         if nf + nt > 0:
             feat = _fe.specaug_apply(feat[None], table, nf, nt)[0]

@@ -41,10 +41,6 @@ class FeatureFrontend:
                  device: Union[None, int, str, torch.device] = None):
         if audio_feature_type not in _lib.FEATURE_TYPES:
             raise ValueError("audio_feature_type must be one of %s" % sorted(_lib.FEATURE_TYPES))
-        if _sa_get(spec_augment, "W"):
-            raise NotImplementedError(
-                "SpecAugment time warping (data.py:275-280) is outside this front-end's scope; "
-                "set W to null as every shipped config does")
         if not torch.cuda.is_available():
             raise RuntimeError("speech_recognition_b200 needs a CUDA device: there is no CPU fallback")
         dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
@@ -54,6 +50,26 @@ class FeatureFrontend:
             dev = torch.device("cuda", torch.cuda.current_device())
         self.device = dev
         sa_on = bool(_sa_get(spec_augment, "enable")) if spec_augment is not None else False
+        # SpecAugment time warping (data.py:275-280; W is null in every shipped config): the warp sits between
+        # the feature and the masks, so the stages run one after the other - feature (the fused kernel of an
+        # inner front-end without masks and deltas), b200mel_time_warp, masks, deltas - instead of in one launch
+        self._warp_W = int(_sa_get(spec_augment, "W") or 0) if sa_on else 0
+        self._inner = None
+        if self._warp_W:
+            self._inner = FeatureFrontend(audio_feature_type, sample_rate, frame_length, frame_step, fft_length,
+                                          num_mel_bins, num_mfcc, lower_edge_hertz, upper_edge_hertz, epsilon,
+                                          use_delta_accelerate=False, spec_augment=None, device=dev)
+            self._handle = None
+            self._sa = {k: _sa_get(spec_augment, k) for k in ("F", "m_F", "T", "p", "m_T")}
+            self._delta = bool(use_delta_accelerate)
+            self.frequency_dim, self.fft_length = self._inner.frequency_dim, self._inner.fft_length
+            self.feature_dim = 3 if use_delta_accelerate else 1
+            self.audio_feature_type = audio_feature_type
+            self.frame_length, self.frame_step = int(frame_length), int(frame_step)
+            self.spec_augment_enabled = True
+            self.num_freq_masks = int(self._sa["m_F"]) if all([self._sa["F"], self._sa["m_F"]]) else 0
+            self.num_time_masks = int(self._sa["m_T"]) if all([self._sa["T"], self._sa["p"], self._sa["m_T"]]) else 0
+            return
         cfg = _lib.B200MelConfig()
         cfg.struct_size = ctypes.sizeof(_lib.B200MelConfig)
         cfg.audio_feature_type = _lib.FEATURE_TYPES[audio_feature_type]
@@ -109,19 +125,27 @@ class FeatureFrontend:
 
     # ------------------------------------------------------------------------------------------
     def num_frames(self, n_samples: int) -> int:
+        if self._inner is not None:
+            return self._inner.num_frames(n_samples)
         out = ctypes.c_int64()
         _lib.check(_lib.load().b200mel_num_frames(self._handle, int(n_samples), ctypes.byref(out)))
         return out.value
 
     @property
     def tc_supported(self) -> bool:
+        if self._inner is not None:
+            return self._inner.tc_supported
         return bool(_lib.load().b200mel_tc_supported(self._handle))
 
     @property
     def launch_count(self) -> int:
+        if self._inner is not None:
+            return self._inner.launch_count
         return int(_lib.load().b200mel_launch_count(self._handle))
 
     def mel_weights(self) -> np.ndarray:
+        if self._inner is not None:
+            return self._inner.mel_weights()
         k = self.fft_length // 2 + 1
         out = np.zeros((k, self._cfg.num_mel_bins), dtype=np.float32)
         _lib.check(_lib.load().b200mel_mel_weights(self._handle, out.ctypes.data_as(ctypes.c_void_p)))
@@ -148,6 +172,9 @@ class FeatureFrontend:
         ``F`` above the feature width, an utterance with fewer frames than a drawn ``t``) leave that
         mask empty and set bit 0 of the device status word: pass ``return_status=True`` and read it
         to get the reference's error behaviour; ``forward_host`` does this itself and raises."""
+        if self._inner is not None:
+            return self._call_with_time_warp(pcm, lengths, offsets, t_max, seed, first_utterance_id, mask_table, out,
+                                             kernel, return_status, validate, n_frames)
         if not pcm.is_cuda or pcm.device != self.device:
             raise RuntimeError("pcm must live on %s (got %s): there is no CPU path" % (self.device, pcm.device))
         if pcm.dtype == torch.int16:
@@ -239,6 +266,32 @@ class FeatureFrontend:
             return out, n_frames, status
         return out, n_frames
 
+    def _call_with_time_warp(self, pcm, lengths, offsets, t_max, seed, first_utterance_id, mask_table, out, kernel,
+                             return_status, validate, n_frames):
+        """The reference's stage order with W set (run/train.py:88-116, data.py:275-301): feature ->
+        time warp -> masks -> deltas, one launch each.  The mask draws need the frame counts on the host
+        (one synchronisation) - this path is for configs that turn W on; none of the shipped ones does."""
+        feats, nf, st = self._inner(pcm, lengths=lengths, offsets=offsets, t_max=t_max, kernel=kernel,
+                                    validate=validate, n_frames=n_frames, return_status=True)
+        feats, st_w = time_warp(feats, nf, self._warp_W, seed, first_utterance_id)
+        st |= st_w
+        sa = self._sa
+        if self.num_freq_masks + self.num_time_masks > 0:
+            if mask_table is None:
+                mask_table, _, _, st_m = specaug_draw(nf.cpu().numpy(), self.frequency_dim, sa["F"], sa["m_F"], sa["T"],
+                                                      sa["p"], sa["m_T"], seed, first_utterance_id, self.device)
+                st |= st_m
+            feats = specaug_apply(feats, mask_table.to(device=self.device, dtype=torch.int32), self.num_freq_masks,
+                                  self.num_time_masks)
+        if self._delta:
+            feats = delta(feats, nf)
+        if out is not None:
+            out.copy_(feats)
+            feats = out
+        if return_status:
+            return feats, nf, st
+        return feats, nf
+
     # ------------------------------------------------------------------------------------------
     def bind(self, pcm: torch.Tensor, lengths: torch.Tensor, out: torch.Tensor, n_frames: torch.Tensor,
              offsets: Optional[torch.Tensor] = None, seed: int = 0, first_utterance_id: int = 0,
@@ -251,6 +304,8 @@ class FeatureFrontend:
         instead of ~17 us of argument handling - that matters when the kernel is 75 us and the timed
         region starts on an idle GPU.  The callable keeps the tensors alive; results land in ``out`` /
         ``n_frames`` (and ``status``, OR-ed, when given) exactly as with ``__call__``."""
+        if self._inner is not None:
+            raise NotImplementedError("bind() is the single-launch form; with time warping (W) call the front-end")
         if kernel not in _lib.KERNELS:
             raise ValueError("kernel must be one of %s" % sorted(_lib.KERNELS))
         for name, t, dt in (("pcm", pcm, None), ("lengths", lengths, torch.int32), ("out", out, torch.float32),
@@ -325,6 +380,9 @@ class FeatureFrontend:
         Submitting step i+1 on the other slot before waiting for step i overlaps its uploads with step i's
         downloads (both directions of the link busy), like the reference's ``prefetch`` (run/train.py:194).
         Pinned buffers are needed for the calls to be asynchronous."""
+        if self._inner is not None:
+            raise NotImplementedError("the host-buffer call is the single-launch form; with time warping (W) call the "
+                                      "front-end on device tensors")
         pcm_np = pcm.numpy() if isinstance(pcm, torch.Tensor) else np.asarray(pcm)
         if pcm_np.dtype == np.int16:
             dt = _lib.PCM_I16
@@ -402,6 +460,29 @@ def specaug_apply(feat: torch.Tensor, table: torch.Tensor, n_freq: int, n_time: 
     _lib.check(_lib.load().b200mel_specaug_apply(_ptr(feat), _ptr(out), B, T, v, C, _ptr(table.contiguous()),
                                                  n_freq, n_time, ctypes.c_void_p(stream)))
     return out
+
+
+def time_warp(feat: torch.Tensor, n_frames, W: int, seed: int = 0, first_utterance_id: int = 0,
+              warp_table: Optional[torch.Tensor] = None) -> Tuple[torch.Tensor, torch.Tensor]:
+    """SpecAugment time warp (data.py:275-280) of feat [B, T, v, C] float32 CUDA, per utterance over its own
+    n_frames[b] rows.  Returns (warped copy, status int32[1]: bit 0 = an utterance too short for the
+    reference's draw was copied unchanged).  ``warp_table`` int32 [B, 2] = (src_t, dst_t) replaces the draws."""
+    feat = feat.contiguous()
+    B, T, v, C = feat.shape
+    nf = torch.as_tensor(n_frames).to(device=feat.device, dtype=torch.int32).contiguous()
+    if nf.shape != (B,):
+        raise ValueError("n_frames must have shape [B]")
+    if warp_table is not None:
+        warp_table = warp_table.to(device=feat.device, dtype=torch.int32).contiguous()
+        if warp_table.shape != (B, 2):
+            raise ValueError("warp_table must be int32 [B, 2]")
+    out = torch.empty_like(feat)
+    status = torch.zeros((1,), dtype=torch.int32, device=feat.device)
+    stream = torch.cuda.current_stream(feat.device).cuda_stream
+    _lib.check(_lib.load().b200mel_time_warp(_ptr(feat), _ptr(out), _ptr(nf), B, T, v, C, int(W or 0), _ptr(warp_table),
+                                             seed & 0xFFFFFFFFFFFFFFFF, first_utterance_id & 0xFFFFFFFFFFFFFFFF,
+                                             _ptr(status), ctypes.c_void_p(stream)))
+    return out, status
 
 
 def delta(feat: torch.Tensor, n_frames: Optional[torch.Tensor] = None) -> torch.Tensor:

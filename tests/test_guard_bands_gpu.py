@@ -167,3 +167,26 @@ def test_rows_either_side_stay_inside(pkg, audio):
     feats, _ = fe(torch.from_numpy(x[:16]).to(dev), lengths=torch.from_numpy(lengths[:16]).to(dev))
     m = batching.audio_mask(feats, [11, 11], [2, 1])
     assert m.dtype == torch.bool or m.dtype == torch.uint8
+
+
+def test_time_warp_stays_inside(pkg, audio):
+    """b200mel_time_warp (N4): guard bands around its output, padding rows written as +0.0."""
+    import ctypes
+
+    from speech_recognition_b200 import _lib
+
+    dev = torch.device("cuda:0")
+    Bw, T, v = 6, 300, 80
+    nf = torch.tensor([300, 299, 150, 81, 2, 0], dtype=torch.int32, device=dev)
+    feat = torch.randn((Bw, T, v, 1), device=dev)
+    out, whole, n = _banded((Bw, T, v, 1), torch.float32, POISON_F, dev)
+    st = torch.zeros(1, dtype=torch.int32, device=dev)
+    rc = _lib.load().b200mel_time_warp(ctypes.c_void_p(feat.data_ptr()), ctypes.c_void_p(out.data_ptr()),
+                                       ctypes.c_void_p(nf.data_ptr()), Bw, T, v, 1, 40, None, 43, 0,
+                                       ctypes.c_void_p(st.data_ptr()), ctypes.c_void_p(torch.cuda.current_stream().cuda_stream))
+    torch.cuda.synchronize()
+    assert rc == 0, _lib.last_error()
+    assert _bands_intact(whole, n, POISON_F)
+    assert not torch.isnan(out).any()
+    for b in range(Bw):
+        assert not out[b, int(nf[b]):].any()
