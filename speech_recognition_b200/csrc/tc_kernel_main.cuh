@@ -935,74 +935,66 @@ __global__ void __launch_bounds__(kTcThreads, 1)
         }
       } else {
         tc::named_bar_sync(14, kTcEpilogueThreads);  // staged (and masked) rows visible to the 12 epilogue warps
-        // ---- copy-out with delta / delta-delta: staged tile -> HBM.  A work item is a PAIR of float4
-        //      groups of one row (8 mel bins): its 24 outputs are 96 contiguous bytes = three whole 32-byte
-        //      sectors, written with three 256-bit stores (the first version wrote 48 bytes per item with
-        //      128-bit stores: every sector arrived at L2 in two halves).  128 rows x 10 pairs = 1280 items
-        //      over 384 threads; the next item's six shared-memory loads are issued before the current
-        //      item's arithmetic and stores (a shared-memory round trip costs >100 cycles while the MMAs
-        //      stream their operands). ----
+        // ---- copy-out with delta / delta-delta: staged tile -> HBM.  A work unit is a PAIR of float4 groups
+        //      (8 mel bins) over a RUN of four consecutive rows: per row its 24 outputs are 96 contiguous bytes =
+        //      three whole 32-byte sectors, written with three 256-bit stores, and the two rows before it stay
+        //      in registers - every staged value is read once per run (1.5 times on average) instead of three
+        //      times.  126 rows = 32 runs x 10 pairs = 320 units over the 384 epilogue threads; the next row's
+        //      two shared-memory loads are issued before the current row's arithmetic and stores (a
+        //      shared-memory round trip costs >100 cycles while the MMAs stream their operands).
+        //      (First version: one (row, pair) item at a time, six loads per item: 135.1 us per config-2 + delta
+        //      batch.) ----
         float* out_b = p.out + static_cast<int64_t>(b) * p.t_max * 240;
-        float4 cx[2][6];
-        bool c_store[2];
-        float* c_dst[2];
-#define TC_CO_LOAD(S, IT)                                                                              \
+        for (int u = etid; u < 320; u += kTcEpilogueThreads) {
+          const int q = u / 10, pr = u - 10 * q;
+          const int i0 = tp.halo + 4 * q;                    // first staged row of the run (halo = 2: rows 2..127)
+          const int t0 = t_first + 4 * q;                    // its frame
+          const float* col = sOut + 8 * pr;
+          float* dst = out_b + (static_cast<int64_t>(t0) * 80 + 8 * pr) * 3;
+          const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+          float4 w2[2], w1[2], w0[2], nx[2];
+          // staged row i holds frame t_first - halo + i: real frames only, everything else reads as zero
+#define TC_CO_ROW(V, I)                                                                                \
   {                                                                                                    \
-    const int item = etid + kTcEpilogueThreads * (IT);                                                 \
-    const int i = item / 10, pr = item - 10 * i;                                                       \
-    const int t = t_first - tp.halo + i;                                                               \
-    c_store[S] = item < 1280 && i >= tp.halo && t < p.t_max;                                           \
-    c_dst[S] = out_b + (static_cast<int64_t>(t) * 80 + 8 * pr) * 3;                                    \
-    const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);                                                 \
-    _Pragma("unroll") for (int k = 0; k < 6; ++k) cx[S][k] = z4;                                       \
-    if (c_store[S] && t < n_fr) {                                                                      \
-      const float* r0 = sOut + i * kTcOutPitch + 8 * pr;                                               \
-      cx[S][0] = *reinterpret_cast<const float4*>(r0);                                                 \
-      cx[S][1] = *reinterpret_cast<const float4*>(r0 + 4);                                             \
-      if (t >= 1) {                                                                                    \
-        cx[S][2] = *reinterpret_cast<const float4*>(r0 - kTcOutPitch);                                 \
-        cx[S][3] = *reinterpret_cast<const float4*>(r0 - kTcOutPitch + 4);                             \
-      }                                                                                                \
-      if (t >= 2) {                                                                                    \
-        cx[S][4] = *reinterpret_cast<const float4*>(r0 - 2 * kTcOutPitch);                             \
-        cx[S][5] = *reinterpret_cast<const float4*>(r0 - 2 * kTcOutPitch + 4);                         \
-      }                                                                                                \
+    const int tt = t_first - tp.halo + (I);                                                            \
+    if (tt >= 0 && tt < n_fr) {                                                                        \
+      V[0] = *reinterpret_cast<const float4*>(col + (I) * kTcOutPitch);                                \
+      V[1] = *reinterpret_cast<const float4*>(col + (I) * kTcOutPitch + 4);                            \
+    } else {                                                                                           \
+      V[0] = z4;                                                                                       \
+      V[1] = z4;                                                                                       \
     }                                                                                                  \
   }
-        // (x, x - x1, (x - x1) - (x1 - x2)) per bin, interleaved [.., m, 3]
-#define TC_CO_STORE(S)                                                                                 \
-  if (c_store[S]) {                                                                                    \
-    const float x0[8] = {cx[S][0].x, cx[S][0].y, cx[S][0].z, cx[S][0].w, cx[S][1].x, cx[S][1].y, cx[S][1].z, cx[S][1].w}; \
-    const float x1[8] = {cx[S][2].x, cx[S][2].y, cx[S][2].z, cx[S][2].w, cx[S][3].x, cx[S][3].y, cx[S][3].z, cx[S][3].w}; \
-    const float x2[8] = {cx[S][4].x, cx[S][4].y, cx[S][4].z, cx[S][4].w, cx[S][5].x, cx[S][5].y, cx[S][5].z, cx[S][5].w}; \
-    float o[24];                                                                                       \
-    _Pragma("unroll") for (int m = 0; m < 8; ++m) {                                                    \
-      const float dd = x0[m] - x1[m], e = x1[m] - x2[m];                                               \
-      o[3 * m] = x0[m];                                                                                \
-      o[3 * m + 1] = dd;                                                                               \
-      o[3 * m + 2] = dd - e;                                                                           \
-    }                                                                                                  \
-    tc::st_global_v8(c_dst[S], o);                                                                     \
-    tc::st_global_v8(c_dst[S] + 8, o + 8);                                                             \
-    tc::st_global_v8(c_dst[S] + 16, o + 16);                                                           \
-  }
-        // 1280 items over 384 threads (4 rounds, the last one partial) or 256 threads (5 rounds)
-        TC_CO_LOAD(0, 0)
-        TC_CO_LOAD(1, 1)
-        TC_CO_STORE(0)
-        TC_CO_LOAD(0, 2)
-        TC_CO_STORE(1)
-        TC_CO_LOAD(1, 3)
-        TC_CO_STORE(0)
-#if TC_NGROUPS == 2
-        TC_CO_LOAD(0, 4)
-        TC_CO_STORE(1)
-        TC_CO_STORE(0)
-#else
-        TC_CO_STORE(1)
-#endif
-#undef TC_CO_LOAD
-#undef TC_CO_STORE
+          TC_CO_ROW(w2, i0 - 2)
+          TC_CO_ROW(w1, i0 - 1)
+          TC_CO_ROW(w0, i0)
+#pragma unroll
+          for (int c = 0; c < 4; ++c) {
+            const int i = i0 + c, t = t0 + c;
+            if (i >= kTcTileM || t >= p.t_max) break;
+            if (c < 3 && i + 1 < kTcTileM) TC_CO_ROW(nx, i + 1)
+            // (x, x - x1, (x - x1) - (x1 - x2)) per bin, interleaved [.., m, 3]; padding frames are +0.0
+            const bool live = t < n_fr;
+            const float x0[8] = {w0[0].x, w0[0].y, w0[0].z, w0[0].w, w0[1].x, w0[1].y, w0[1].z, w0[1].w};
+            const float x1[8] = {w1[0].x, w1[0].y, w1[0].z, w1[0].w, w1[1].x, w1[1].y, w1[1].z, w1[1].w};
+            const float x2[8] = {w2[0].x, w2[0].y, w2[0].z, w2[0].w, w2[1].x, w2[1].y, w2[1].z, w2[1].w};
+            float o[24];
+#pragma unroll
+            for (int m = 0; m < 8; ++m) {
+              const float dd = x0[m] - x1[m], e = x1[m] - x2[m];
+              o[3 * m] = live ? x0[m] : 0.0f;
+              o[3 * m + 1] = live ? dd : 0.0f;
+              o[3 * m + 2] = live ? dd - e : 0.0f;
+            }
+            tc::st_global_v8(dst + 240 * c, o);
+            tc::st_global_v8(dst + 240 * c + 8, o + 8);
+            tc::st_global_v8(dst + 240 * c + 16, o + 16);
+            w2[0] = w1[0]; w2[1] = w1[1];
+            w1[0] = w0[0]; w1[1] = w0[1];
+            w0[0] = nx[0]; w0[1] = nx[1];
+          }
+#undef TC_CO_ROW
+        }
         tc::named_bar_sync(14, kTcEpilogueThreads);  // the staging tile and the hand-over zone may be overwritten
       }
     }
