@@ -467,6 +467,11 @@ def main():
     # clock / power-state ramp: NVML start-up above leaves the GPU idle for tens of ms; untimed passes of the
     # same step bring SM and HBM clocks back to their loaded state before the W warm-up steps
     n_spin = 0
+    if dist is not None and not os.environ.get("B200MEL_BENCH_NO_ALIGN"):
+        # align the ranks BEFORE the untimed steps: the mandated barrier in front of the timed region is then
+        # reached by all ranks within microseconds, and no GPU sits idle for milliseconds right before it is timed
+        dist.barrier()
+        torch.cuda.synchronize()
     if args.spin_up_ms > 0:
         t_spin = time.perf_counter()
         while (time.perf_counter() - t_spin) * 1e3 < args.spin_up_ms:
