@@ -23,7 +23,9 @@ ev = {0: ["start", "w0", "w1", "w2", "w3", "arr_w4", "done", "arr_w7"], 1: ["top
       2: ["top", "accfull", "released", "loopend", "", "done", "", ""], 3: ["top", "accfull", "released", "loopend", "phase1", "done", "bar_ab", ""],
       4: ["top", "accfull", "released", "loopend", "phase1", "done", "bar_bc", "stored"]}
 print("kernel: top=%d setup_done=%d dep_wait_done=%d teardown=%d" % tuple(t[1, 31, e] - t0 for e in range(4)))
+print("list (epilogue thread 0): enter=%d ranges_known=%d written=%d list_full_seen=%d" % tuple(t[2, 30, e] - t0 for e in range(4)))
 t[1, 31, :] = 0
+t[2, 30, :] = 0
 for n in list(range(0, 2)) + list(range(9, 12)) + list(range(20, 21)):
     print("tile", n)
     for r in range(5):

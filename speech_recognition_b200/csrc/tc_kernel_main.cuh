@@ -674,6 +674,7 @@ __global__ void __launch_bounds__(kTcThreads, 1)
       //      the index of its first active tile, and it writes those of its tiles that fall into this
       //      CTA's range.  Ready ~one L2 round trip after the kernel starts. ----
       const int ew = warp - 8;
+      if (etid == 0) { TC_STAMP_F(2, 30, 0) }
       int32_t* nfo = reporter ? p.n_frames : nullptr;
       int32_t* sfe = (reporter && p.n_masks_t > 0) ? p.status : nullptr;
       long long total = 0;
@@ -708,6 +709,7 @@ __global__ void __launch_bounds__(kTcThreads, 1)
         a1r = (total * (blockIdx.x + 1)) / gridDim.x;
       }
       const long long a1 = a1r - a0 > kTcListTiles ? a0 + kTcListTiles : a1r;  // (the host keeps ranges within the list)
+      if (etid == 0) { TC_STAMP_F(2, 30, 1) }
       if (ew == 0 && lane == 0) ctl->n_tiles = static_cast<int32_t>(a1 - a0);
       long long acc = 0;
       for (int base = 0; base < batch_eff; base += 256) {
@@ -746,9 +748,11 @@ __global__ void __launch_bounds__(kTcThreads, 1)
         }
       }
       __syncwarp();
+      if (etid == 0) { TC_STAMP_F(2, 30, 2) }
       if (lane == 0) tc::mbar_arrive(&ctl->list_full);
     }
     if (!tc::mbar_wait(&ctl->list_full, 0)) timed_out = true;
+    if (etid == 0) { TC_STAMP_F(2, 30, 3) }
     const int n_tiles = ctl->n_tiles;
     if (n_masks > 0 && !p.mask_table) {
       TcDrawArgs da;
