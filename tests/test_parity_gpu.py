@@ -563,3 +563,26 @@ def test_large_batch_properties(fe_mod):
     assert torch.equal(out[0::2, 1:], out[1::2, :-1])          # shift by one hop == shift by one frame
     x = batch[37].astype(np.float64) / 32768.0
     assert_logmel_close(out[37].cpu().numpy(), O.make_log_mel_spectrogram(x, **LIBRI, dtype=np.float64), what="b=37")
+
+
+def test_more_than_256_utterances_in_one_launch(fe_mod):
+    """The tile list is built in chunks of 256 utterances (one per thread of the eight list-building warps, the
+    warps' sums exchanged through shared memory): 700 ragged utterances = three chunks, the last one partial,
+    with utterances that have no frame at all in between.  Tensor-core kernel against the generic kernel
+    (same tolerance as the other tc-vs-generic checks), frame counts exact, padding exactly zero; C = 1 and 3."""
+    rng = np.random.default_rng(77)
+    B, L = 700, 9600
+    x = np.clip(np.rint(rng.standard_normal((B, L)) * 3000.0), -32768, 32767).astype(np.int16)
+    lengths = rng.integers(320, L + 1, B).astype(np.int32)
+    lengths[[0, 255, 256, 511, 512, 699]] = [L, 319, L, 100, 4000, L]      # chunk borders; two utterances without a frame
+    for delta in (False, True):
+        fe = fe_mod.FeatureFrontend("log-mel-spectrogram", **LIBRI, use_delta_accelerate=delta)
+        a, nfa, st = fe(dev(x), lengths=lengths, kernel="tc", return_status=True)
+        b, nfb = fe(dev(x), lengths=lengths, kernel="generic")
+        assert int(st.item()) == 0
+        want_nf = np.maximum(0, 1 + (lengths.astype(np.int64) - 320) // 160)
+        assert np.array_equal(nfa.cpu().numpy(), want_nf) and torch.equal(nfa, nfb)
+        assert (a - b).abs().max().item() <= (4e-2 if delta else 2e-2)
+        a = a.cpu().numpy()
+        for i in (0, 255, 256, 300, 511, 512, 699):
+            assert not a[i, want_nf[i]:].any()
