@@ -67,7 +67,7 @@ typedef struct b200mel_config {
   float upper_edge_hertz;
   float epsilon;                /* data.py:153 default 1e-12 */
   int32_t use_delta_accelerate; /* delta_accelerate, data.py:310-328: C = 3 instead of 1 */
-  /* SpecAugmentConfig (configs/data_config.py:10-20); W (time warp) is not supported */
+  /* SpecAugmentConfig (configs/data_config.py:10-20); W (time warp) is a separate stage: b200mel_time_warp */
   int32_t spec_augment_enable;
   int32_t sa_F, sa_m_F;         /* frequency masking, data.py:282-288 */
   int32_t sa_T, sa_m_T;         /* time masking, data.py:290-301 */
