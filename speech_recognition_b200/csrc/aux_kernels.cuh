@@ -279,7 +279,10 @@ __global__ void __launch_bounds__(kMfccThreads)
 // count: the kernel is bound by the legacy tensor path, ~160 TF32 MAC per clock and SM); f16 m16n8k16
 // (half the instructions, twice the MACs each): see DESIGN.
 // ---------------------------------------------------------------------------------------------
-constexpr int kMfccMmaRows = 128, kMfccMmaThreads = 256, kMfccMmaM = 80;
+#ifndef MFCC_MMA_BLOCKS
+#define MFCC_MMA_BLOCKS 3   // resident blocks per SM the kernel is compiled for (register cap 65536 / (256 x blocks))
+#endif
+constexpr int kMfccMmaRows = 128, kMfccMmaThreads = 256, kMfccMmaM = 80, kMfccMmaBlocksPerSm = MFCC_MMA_BLOCKS;
 __host__ __device__ constexpr int mfcc_mma_pitch(int n_mfcc) {   // coefficient rows in shared memory (floats)
   int p = n_mfcc;
   while ((p & 31) != 8 && (p & 31) != 24) ++p;
@@ -325,7 +328,7 @@ __device__ __forceinline__ void mfcc_st_v8(float* p, const float* v) {
 }
 
 template <int NT, int C>
-__global__ void __launch_bounds__(kMfccMmaThreads, 3)
+__global__ void __launch_bounds__(kMfccMmaThreads, MFCC_MMA_BLOCKS)
     mfcc_post_mma_kernel(const float* __restrict__ lm, float* __restrict__ out, const int32_t* __restrict__ lengths,
                          int batch, int64_t t_max, int Lw, int H, const uint32_t* __restrict__ dct_image, int reverse,
                          int n_masks_f, int n_masks_t, int sa_F, int sa_T, float sa_p,

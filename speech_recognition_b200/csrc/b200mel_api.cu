@@ -77,7 +77,7 @@ cudaError_t mfcc_mma_do(int what, int max_smem_optin, const MfccMmaArgs& a, cuda
   // one resident wave: three blocks per SM, each a contiguous run of the batch's tiles
   // (walked from the end: the rows the first stage wrote last are still in L2 - r2t: 137.5 vs 138.5 us)
   static const int rev = [] { const char* e = std::getenv("B200MEL_MFCC_REVERSE"); return e ? std::atoi(e) : 1; }();
-  const int64_t slots = 3LL * a.sm_count;
+  const int64_t slots = static_cast<int64_t>(kMfccMmaBlocksPerSm) * a.sm_count;
   dim3 grid(static_cast<unsigned>(tiles < slots ? tiles : slots));
   kernel<<<grid, kMfccMmaThreads, mfcc_post_mma_smem_bytes(8 * NT), st>>>(
       a.lm, a.out, a.lengths, a.batch, a.t_max, a.Lw, a.H, a.dct_image, rev, a.n_masks_f, a.n_masks_t,
