@@ -52,3 +52,31 @@ def test_submit_wait_matches_synchronous_call(built_lib, delta):
     assert outs[1].numpy().tobytes() == want[1][0].tobytes()
     with pytest.raises(ValueError):
         fe.forward_host_submit(ins[0], out=outs[0], slot=2)
+
+
+@pytest.mark.gpu
+def test_bound_step_equals_the_call(built_lib):
+    """FeatureFrontend.bind: arguments checked once, the returned callable is the b200mel_forward call alone."""
+    import speech_recognition_b200 as pkg
+
+    sa = dict(enable=True, F=27, m_F=2, T=100, p=1.0, m_T=2)
+    fe = pkg.FeatureFrontend("log-mel-spectrogram", **LIBRI, use_delta_accelerate=True, spec_augment=sa)
+    B, L = 5, 48000
+    pcm = torch.from_numpy(np.stack([noise_int16(L, 40 + i) for i in range(B)])).cuda()
+    lengths = torch.tensor([48000, 47999, 20000, 320, 100], dtype=torch.int32, device="cuda")
+    want, nf, st = fe(pcm, lengths=lengths, seed=7, first_utterance_id=3, return_status=True)
+    out = torch.full_like(want, float("nan"))
+    nf2 = torch.zeros_like(nf)
+    status = torch.zeros(1, dtype=torch.int32, device="cuda")
+    step = fe.bind(pcm, lengths, out, nf2, seed=7, first_utterance_id=3, status=status)
+    step()
+    step()                                                        # (a second time: same buffers, same result)
+    torch.cuda.synchronize()
+    assert torch.equal(out, want) and torch.equal(nf2, nf)
+    assert int(status.item()) == int(st.item())                   # (utterance 4 has no frame: its time-mask draw is refused, bit 0)
+    with pytest.raises(ValueError):
+        fe.bind(pcm, lengths.to(torch.int64), out, nf2)
+    with pytest.raises(ValueError):
+        fe.bind(pcm, lengths, out[:, :10], nf2)
+    with pytest.raises(ValueError):
+        fe.bind(pcm.cpu(), lengths, out, nf2)
