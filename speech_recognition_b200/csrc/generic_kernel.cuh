@@ -77,8 +77,9 @@ __device__ __forceinline__ void stockham_pass(const float2* __restrict__ in, flo
                                               int Nc, int Ns, const float2* __restrict__ tw, int lane) {
   const int m = Nc / R;
   const int tstride = Nc / (Ns * R);
+  const bool ns_pow2 = (Ns & (Ns - 1)) == 0;   // (true for every pass of a power-of-two transform: no division per element)
   for (int j = lane; j < m; j += 32) {
-    const int k = j % Ns;
+    const int k = ns_pow2 ? (j & (Ns - 1)) : j % Ns;
     float2 v[R];
 #pragma unroll
     for (int q = 0; q < R; ++q) v[q] = in[j + q * m];
@@ -246,39 +247,44 @@ __global__ void __launch_bounds__(256) generic_frontend_kernel(const KernelParam
   const int rows = static_cast<int>(t_end - t0);
   const int64_t total = static_cast<int64_t>(rows) * F * C;
   float* outp = p.out + (static_cast<int64_t>(b) * p.t_max + t0) * F * C;
-  for (int64_t o = threadIdx.x; o < total; o += blockDim.x) {
-    const int c = static_cast<int>(o % C);
-    const int e = static_cast<int>(o / C);
-    const int j = e % F;
-    const int i = e / F;
+  // one row per warp at a time, the row's F * C outputs over the lanes: no 64-bit division per element
+  // (the first version walked the flat index with o % C, o / C, e % F, e / F per output)
+  (void)total;
+  const int FC = F * C;
+  for (int i = warp; i < rows; i += p.warps) {
     const int t = t0 + i;
-    float val = 0.0f;
-    if (t < n_fr) {
-      const float* r0 = tile_feat + static_cast<size_t>(i + halo) * F + j;
-      float x0 = r0[0];
-      if (n_masks) x0 *= mask_value(s_table, p.n_masks_f, p.n_masks_t, t, j);
-      if (c == 0) {
-        val = x0;
-      } else {
-        float x1 = 0.0f, x2 = 0.0f;
-        if (t >= 1) {
-          x1 = r0[-F];
-          if (n_masks) x1 *= mask_value(s_table, p.n_masks_f, p.n_masks_t, t - 1, j);
-        }
-        float d0 = x0 - x1;
-        if (c == 1) {
-          val = d0;
+    float* orow = outp + static_cast<int64_t>(i) * FC;
+    for (int e = lane; e < FC; e += 32) {
+      const int j = C == 3 ? e / 3 : (C == 1 ? e : e / C);
+      const int c = e - j * C;
+      float val = 0.0f;
+      if (t < n_fr) {
+        const float* r0 = tile_feat + static_cast<size_t>(i + halo) * F + j;
+        float x0 = r0[0];
+        if (n_masks) x0 *= mask_value(s_table, p.n_masks_f, p.n_masks_t, t, j);
+        if (c == 0) {
+          val = x0;
         } else {
-          if (t >= 2) {
-            x2 = r0[-2 * F];
-            if (n_masks) x2 *= mask_value(s_table, p.n_masks_f, p.n_masks_t, t - 2, j);
+          float x1 = 0.0f, x2 = 0.0f;
+          if (t >= 1) {
+            x1 = r0[-F];
+            if (n_masks) x1 *= mask_value(s_table, p.n_masks_f, p.n_masks_t, t - 1, j);
           }
-          float d1 = x1 - x2;
-          val = d0 - d1;
+          float d0 = x0 - x1;
+          if (c == 1) {
+            val = d0;
+          } else {
+            if (t >= 2) {
+              x2 = r0[-2 * F];
+              if (n_masks) x2 *= mask_value(s_table, p.n_masks_f, p.n_masks_t, t - 2, j);
+            }
+            float d1 = x1 - x2;
+            val = d0 - d1;
+          }
         }
       }
+      orow[e] = val;
     }
-    outp[o] = val;
   }
 }
 
